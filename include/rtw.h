@@ -1,0 +1,306 @@
+/*
+ * rtw.h — C-ABI of the B200-native wavefront path tracer.
+ *
+ * This header is the drop-in boundary of the hot path.  The
+ * reference has no FFI of its own; the narrowest seam is the `Director` class
+ * (reference RestOfLife/Director.h:118-126) driven from RestOfLife/main.cpp:145-164.
+ * Every entry point below names the reference interface it replaces.
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no C++/torch types, no exceptions, no exit().
+ *   - every function returns an int status (RTW_OK == 0); rtw_last_error()
+ *     returns a human readable string for the last failure on that context.
+ *   - host arrays passed in are borrowed for the duration of the call only.
+ *   - a context is bound to ONE CUDA device and is not thread-safe.
+ *   - there is NO CPU fallback: without a usable CUDA device rtw_create fails
+ *     with RTW_ERR_NO_DEVICE.
+ *
+ * All arithmetic is fp32, RNG state is uint32.
+ */
+#ifndef RTW_H
+#define RTW_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTW_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+#define RTW_OK             0
+#define RTW_ERR_INVALID    1   /* bad argument                               */
+#define RTW_ERR_CUDA       2   /* a CUDA runtime call failed                 */
+#define RTW_ERR_NO_DEVICE  3   /* no usable CUDA device (no CPU fallback)    */
+#define RTW_ERR_STATE      4   /* call order violated (e.g. render before build) */
+#define RTW_ERR_IO         5   /* file could not be read / written           */
+
+typedef struct rtw_ctx rtw_ctx;     /* opaque: one CUDA device, one stream set */
+
+/* ---- enumerations ------------------------------------------------------ */
+
+/* Primitive kinds == the reference's intersection programs
+ * (geometry/sphere.cu:48, geometry/movingSphere.cu:61, shaders/aarect{x,y,z}.cu:8,
+ *  geometry/volumeBox.cu:55, geometry/volumeSphere.cu:67). */
+enum rtw_prim_type {
+    RTW_PRIM_SPHERE        = 0,
+    RTW_PRIM_MOVING_SPHERE = 1,
+    RTW_PRIM_RECT_X        = 2,
+    RTW_PRIM_RECT_Y        = 3,
+    RTW_PRIM_RECT_Z        = 4,
+    RTW_PRIM_VOLUME_BOX    = 5,
+    RTW_PRIM_VOLUME_SPHERE = 6,
+    RTW_PRIM_TYPE_COUNT    = 7
+};
+
+/* Material kinds, numbered like MaterialType (lib/raydata.cuh:23-30). */
+enum rtw_material_type {
+    RTW_MAT_LAMBERTIAN    = 0,
+    RTW_MAT_DIFFUSE_LIGHT = 1,
+    RTW_MAT_METAL         = 2,
+    RTW_MAT_DIELECTRIC    = 3,
+    RTW_MAT_ISOTROPIC     = 4,
+    RTW_MAT_NORMAL        = 5,
+    RTW_MAT_TYPE_COUNT    = 6
+};
+
+/* Texture kinds, numbered like TexCallFunction (shaders/FunctionIdx.h:8-15). */
+enum rtw_texture_type {
+    RTW_TEX_CHECKER  = 0,
+    RTW_TEX_CONSTANT = 1,
+    RTW_TEX_IMAGE    = 2,
+    RTW_TEX_NOISE    = 3,
+    RTW_TEX_NULL     = 4,
+    RTW_TEX_TYPE_COUNT = 5
+};
+
+/* ---- scene description (POD, replaces HitGroupData / MaterialParams /
+ *      textureParam / LightDefinition / SysParamter camera fields) --------- */
+
+/* One primitive (reference: one OptixInstance + one HitGroupData record,
+ * lib/raydata.cuh:95-115).  Layout of v[] by type:
+ *   SPHERE         v = cx cy cz r
+ *   MOVING_SPHERE  v = c0x c0y c0z r c1x c1y c1z time0 time1
+ *   RECT_X/Y/Z     v = a0 a1 b0 b1 k            (hitRectData, raydata.cuh:76-84)
+ *   VOLUME_BOX     v = minx miny minz maxx maxy maxz density
+ *   VOLUME_SPHERE  v = cx cy cz r density
+ */
+typedef struct rtw_prim {
+    int32_t type;       /* rtw_prim_type                                       */
+    int32_t material;   /* index into materials (reference: instanceId → MatParams) */
+    int32_t transform;  /* index into transforms, -1 = identity                 */
+    int32_t flip;       /* rect only: normal = -axis (hitRectData.flip)        */
+    float   v[12];
+} rtw_prim;             /* 64 bytes */
+
+/* Instance transform: row-major 3x4 object→world (OptixInstance::transform) and
+ * its inverse world→object (computed by OptiX internally in the reference; by
+ * the host scene builder here). */
+typedef struct rtw_transform {
+    float o2w[12];
+    float w2o[12];
+} rtw_transform;
+
+/* MaterialParams (shaders/sysparameter.h:5-15). */
+typedef struct rtw_material {
+    int32_t type;       /* rtw_material_type */
+    int32_t texture;    /* index into textures, -1 = none (dielectric, normal) */
+    float   param;      /* metal: fuzz (clamped to 1, material/ioMetalMaterial.h:28-32); dielectric: eta */
+    int32_t pad;
+} rtw_material;
+
+/* textureParam (lib/raydata.cuh:127-138). */
+typedef struct rtw_texture {
+    int32_t type;       /* rtw_texture_type */
+    float   color[3];   /* constant */
+    int32_t odd, even;  /* checker: indices into textures (Q18: dispatched correctly) */
+    float   scale;      /* noise */
+    int32_t perlin;     /* noise: index into perlin tables */
+    int32_t image;      /* image: index into images */
+    int32_t pad[3];
+} rtw_texture;          /* 48 bytes */
+
+/* Perlin tables (texture/ioTexture.h:181-216). */
+typedef struct rtw_perlin {
+    float   ranvec[256][3];
+    int32_t perm_x[256];
+    int32_t perm_y[256];
+    int32_t perm_z[256];
+} rtw_perlin;
+
+/* RGBA8 image, row 0 = v == 0 (already flipped like texture/ioTexture.h:247-266). */
+typedef struct rtw_image {
+    int32_t width, height;
+    const uint8_t* rgba;    /* width*height*4 bytes */
+} rtw_image;
+
+/* LightDefinition (lib/raydata.cuh:32-49). */
+typedef struct rtw_light {
+    float position[3];
+    float vecU[3];
+    float vecV[3];
+    float normal[3];
+    float area;
+    float emission[3];
+} rtw_light;
+
+/* The single sampling rectangle of pdf.p1 (scene/ioScene.h:103-148, Q26). */
+typedef struct rtw_light_rect {
+    int32_t axis;           /* 0 = X, 1 = Y, 2 = Z (rect_{x,y,z}_generate) */
+    float   a0, a1, b0, b1, k;
+} rtw_light_rect;
+
+/* Camera fields of SysParamter (shaders/sysparameter.h:44-56). */
+typedef struct rtw_camera {
+    float origin[3];
+    float u[3], v[3], w[3];
+    float lower_left[3];
+    float horizontal[3];
+    float vertical[3];
+    float lens_radius;      /* 0 in every reference scene (Q3) */
+    float time0, time1;
+} rtw_camera;
+
+typedef struct rtw_scene_desc {
+    int32_t n_prims;       const rtw_prim*      prims;
+    int32_t n_transforms;  const rtw_transform* transforms;
+    int32_t n_materials;   const rtw_material*  materials;
+    int32_t n_textures;    const rtw_texture*   textures;
+    int32_t n_perlin;      const rtw_perlin*    perlin;
+    int32_t n_images;      const rtw_image*     images;
+    int32_t n_lights;      const rtw_light*     lights;
+    int32_t has_light_rect; rtw_light_rect      light_rect;
+    rtw_camera camera;
+    int32_t sky_light;      /* Director.cpp:523: true iff the scene has no lights */
+    int32_t reserved;
+} rtw_scene_desc;
+
+/* ---- test-hook PODs ---------------------------------------------------- */
+typedef struct rtw_ray {
+    float origin[3];
+    float tmin;
+    float dir[3];
+    float tmax;
+    float time;         /* ray time (motion transform key interpolation)      */
+    float gather_time;  /* PerRayData::gatherTime (moving sphere centre)      */
+    uint32_t seed;      /* path seed at ray start (constant-medium free flight, Q23) */
+    uint32_t pad;
+} rtw_ray;              /* 48 bytes */
+
+typedef struct rtw_hit {
+    float   t;          /* hit distance, undefined when prim < 0 */
+    int32_t prim;       /* index into rtw_scene_desc::prims, -1 = miss */
+} rtw_hit;
+
+typedef struct rtw_stats {
+    uint64_t paths;             /* camera samples completed by the last render */
+    uint64_t rays_closest;      /* closest-hit traversals                       */
+    uint64_t rays_shadow;       /* any-hit (shadow) traversals                  */
+    uint64_t kernel_launches;   /* kernels launched by the last render          */
+    uint64_t iterations;        /* wavefront iterations of the last render      */
+    double   render_ms;         /* device time of the last render (CUDA events) */
+    double   build_ms;          /* device time of the last rtw_build_accel      */
+    double   traverse_ms;       /* device time inside k_traverse_closest, if profiling was enabled, else 0 */
+    double   shadow_ms;         /* device time inside k_traverse_shadow, ditto  */
+    double   shade_ms;          /* device time inside the shading kernels, ditto */
+    double   logic_ms;          /* device time inside k_logic, ditto            */
+} rtw_stats;
+
+typedef struct rtw_bvh_info {
+    int32_t n_leaves;
+    int32_t n_internal;
+    int32_t root;
+    int32_t n_top;              /* internal nodes staged in shared memory       */
+    float   scene_min[3];
+    float   scene_max[3];
+} rtw_bvh_info;
+
+/* ---- context lifetime (replaces Director::init / destroy,
+ *      Director.cpp:33-104, Director.h:120,126) --------------------------- */
+int  rtw_abi_version(void);
+int  rtw_device_count(int* count);
+int  rtw_create(int device, rtw_ctx** out);
+int  rtw_destroy(rtw_ctx* ctx);
+const char* rtw_last_error(const rtw_ctx* ctx);   /* ctx may be NULL: last create error */
+
+/* ---- scene + acceleration structure (replaces Director::createScene →
+ *      createSBT + initLaunchParams, Director.cpp:483-553,628-885, and every
+ *      optixAccelBuild call site) -------------------------- */
+int  rtw_upload_scene(rtw_ctx* ctx, const rtw_scene_desc* scene);
+int  rtw_build_accel(rtw_ctx* ctx);
+
+/* ---- render (replaces Director::renderFrame's optixLaunch,
+ *      Director.cpp:971-986 → raygen/raygen.cu:123) ----------------------- */
+
+/* Synchronous.  rgba_out_host: caller-owned Nx*Ny*4 floats, row 0 = bottom row,
+ * sqrt-gamma encoded, alpha 1 (raygen/raygen.cu:151-158).  spp == 1 reproduces
+ * the reference launch (Q1); spp > 1 averages samples k = 0..spp-1 whose seeds
+ * are tea<64>(pixel, k). */
+int  rtw_render(rtw_ctx* ctx, int Nx, int Ny, int spp, int max_depth,
+                float* rgba_out_host);
+
+/* Multi-GPU building blocks.  accum_dev is a DEVICE buffer of Nx*Ny float4
+ * holding linear (pre-gamma) radiance sums; it is NOT cleared by the call.
+ * Samples rendered: k = sample_first + i*sample_stride, i = 0..sample_count-1.
+ * Rank g of G uses sample_first = g, sample_stride = G.
+ * Synchronous with respect to the host. */
+int  rtw_render_accum(rtw_ctx* ctx, int Nx, int Ny,
+                      int sample_first, int sample_stride, int sample_count,
+                      int max_depth, float* accum_dev);
+/* out_dev[i] = (sqrt(accum.rgb / spp_total), 1)  (raygen/raygen.cu:144-158) */
+int  rtw_tonemap(rtw_ctx* ctx, int Nx, int Ny, int spp_total,
+                 const float* accum_dev, float* rgba_out_dev);
+/* Copy the linear sums of the last rtw_render (for relMSE, SURVEY.md §8b "Output"). */
+int  rtw_get_linear(rtw_ctx* ctx, float* rgba_linear_mean_host, int n_floats);
+
+/* Tunables: "pool_paths" (wavefront pool size), "top_nodes" (BVH nodes staged in
+ * shared memory), "profile" (per-stage event timing 0/1), "graph" (CUDA graph 0/1). */
+int  rtw_set_option(rtw_ctx* ctx, const char* name, int64_t value);
+int  rtw_get_stats(rtw_ctx* ctx, rtw_stats* out);
+
+/* ---- tier-1 test hooks ---------------------------- */
+/* BVH closest hit / any hit on a caller-supplied ray set (host arrays). */
+int  rtw_trace_closest(rtw_ctx* ctx, const rtw_ray* rays, int n, rtw_hit* hits);
+int  rtw_trace_any(rtw_ctx* ctx, const rtw_ray* rays, int n, int32_t* occluded);
+/* RNG streams computed on the device: s = tea<64>(seed0, seed1); then n steps
+ * of lcg → lcg_out[i], rnd_out[i] (SDK cuda/random.h as restated in SURVEY §8c);
+ * and n steps of xorshift32/randf from the same start → xs_out[i], randf_out[i]
+ * (lib/random.cuh:22-38).  Any output pointer may be NULL. */
+int  rtw_rng_stream(rtw_ctx* ctx, uint32_t seed0, uint32_t seed1, int n,
+                    uint32_t* tea_out, uint32_t* lcg_out, float* rnd_out,
+                    uint32_t* xs_out, float* randf_out);
+/* Sample-0 camera rays as the device generates them (raygen/raygen.cu:129-135,
+ * shaders/camera.cu:11-19); rays_out has Nx*Ny entries. */
+int  rtw_camera_rays(rtw_ctx* ctx, int Nx, int Ny, int sample, rtw_ray* rays_out);
+/* LBVH topology for parity against the host mirror.  Arrays are caller-owned:
+ * morton[n_leaves] (sorted 63-bit codes), leaf_prim[n_leaves] (prim id of leaf i),
+ * left/right[n_internal] (child refs: >=0 internal index, <0 → leaf ~ref),
+ * bounds[n_internal*12] (lmin.xyz lmax.xyz rmin.xyz rmax.xyz).  Any may be NULL. */
+int  rtw_bvh_info_get(rtw_ctx* ctx, rtw_bvh_info* info);
+int  rtw_bvh_download(rtw_ctx* ctx, uint64_t* morton, int32_t* leaf_prim,
+                      int32_t* left, int32_t* right, float* bounds);
+/* Device radix sort hook (the LBVH builder's sort), host arrays in/out. */
+int  rtw_sort_pairs(rtw_ctx* ctx, uint64_t* keys, uint32_t* values, int n);
+
+/* ---- host-side scene flattening (replaces ioScene::init and the scene
+ *      functions, scene/ioScene.h:52-101,180-982; Director.cpp:483-553) ---- */
+typedef struct rtw_scene rtw_scene;
+/* scene_id 0..4 = the reference's scenes; 5 = the synthetic stress scene C5
+ * (n_stress_prims primitives, 0 → 2^20).  asset_dir holds
+ * earthmap.ppm for scenes 2 and 4 (NULL → "assets"). */
+int  rtw_scene_create(int scene_id, int Nx, int Ny, const char* asset_dir,
+                      int n_stress_prims, rtw_scene** out);
+const rtw_scene_desc* rtw_scene_get_desc(const rtw_scene* s);
+const char* rtw_scene_description(const rtw_scene* s);
+void rtw_scene_free(rtw_scene* s);
+
+/* ---- output (replaces Director::printPPM, Director.cpp:1010-1031) ------ */
+/* P3 text, top row first, int(255.99f*clamp(c,0,1)); path NULL or "-" → stdout. */
+int  rtw_write_ppm(const char* path, int Nx, int Ny, const float* rgba);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTW_H */

@@ -1,0 +1,1271 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.h).  PARITY UNPINNED except RNG.
+//
+// Scalar CPU restatement of the reference launch.  One function per reference
+// program; citations are relative to /root/reference/RestOfLife/.
+// Build: g++ -O2 -ffp-contract=off (no fast-math) so every a*b+c rounds twice,
+// exactly as the expression is written.
+#include "oracle.h"
+#include "vecmath.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cfloat>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+using namespace orc;
+
+// ============================================================================
+// RNG
+// ============================================================================
+// lib/random.cuh:7-19 (tea<N>)
+static inline uint32_t tea_n(uint32_t N, uint32_t s0, uint32_t s1) {
+    uint32_t t = 0;
+    for (uint32_t n = 0; n < N; n++) {
+        t += 0x9E3779B9;
+        s0 += ((s1 << 4) + 0xa341316c) ^ (s1 + t) ^ ((s1 >> 5) + 0xc8013ea4);
+        s1 += ((s0 << 4) + 0xad90777d) ^ (s0 + t) ^ ((s0 >> 5) + 0x7e95761e);
+    }
+    return s0;
+}
+// lib/random.cuh:22-28
+static inline uint32_t xorshift32(uint32_t& s) {
+    s ^= s << 13;
+    s ^= s >> 17;
+    s ^= s << 5;
+    return s;
+}
+// lib/random.cuh:31-38.  `return 0x3F7FFFFF;` is an int → float conversion
+// (1065353215.f), kept literally.
+static inline float randf(uint32_t& s) {
+    float r = ((float)xorshift32(s)) / 4294967296.0f;
+    if (r != 1.0f) return r;
+    return (float)0x3F7FFFFF;
+}
+// OptiX SDK 8.0.0 cuda/random.h (not under /root/reference; published recurrence,
+// SURVEY §8c): lcg + rnd.
+static inline uint32_t lcg(uint32_t& prev) {
+    const uint32_t LCG_A = 1664525u;
+    const uint32_t LCG_C = 1013904223u;
+    prev = (LCG_A * prev + LCG_C);
+    return prev & 0x00FFFFFF;
+}
+static inline float rnd(uint32_t& prev) { return ((float)lcg(prev) / (float)0x01000000); }
+
+extern "C" uint32_t orc_tea(uint32_t rounds, uint32_t s0, uint32_t s1) { return tea_n(rounds, s0, s1); }
+
+extern "C" void orc_rng_stream(uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out,
+                               uint32_t* lcg_out, float* rnd_out, uint32_t* xs_out, float* randf_out) {
+    uint32_t s = tea_n(64, seed0, seed1);
+    if (tea_out) *tea_out = s;
+    uint32_t a = s, b = s, c = s, d = s;
+    for (int i = 0; i < n; i++) {
+        if (lcg_out) lcg_out[i] = lcg(a);
+        if (rnd_out) rnd_out[i] = rnd(b);
+        if (xs_out) xs_out[i] = xorshift32(c);
+        if (randf_out) randf_out[i] = randf(d);
+    }
+}
+
+// ============================================================================
+// Scene (deep copy of the C-ABI POD)
+// ============================================================================
+struct Aabb { V3 mn, mx; };
+
+struct BvhNode {          // host mirror of the device LBVH node
+    V3 lmin, lmax, rmin, rmax;
+    int32_t left, right;  // >= 0 internal index, < 0 → leaf ~ref
+    int32_t parent;
+};
+
+struct orc_scene {
+    std::vector<rtw_prim> prims;
+    std::vector<rtw_transform> xforms;
+    std::vector<rtw_material> mats;
+    std::vector<rtw_texture> texs;
+    std::vector<rtw_perlin> perlin;
+    std::vector<rtw_image> images;
+    std::vector<std::vector<uint8_t>> image_data;
+    std::vector<rtw_light> lights;
+    int has_light_rect = 0;
+    rtw_light_rect light_rect{};
+    rtw_camera cam{};
+    int sky_light = 0;
+    // host-mirror LBVH
+    bool bvh_built = false;
+    std::vector<uint64_t> morton;
+    std::vector<int32_t> leaf_prim;
+    std::vector<BvhNode> nodes;
+    Aabb scene_box{};
+};
+
+extern "C" int orc_scene_load(const rtw_scene_desc* d, orc_scene** out) {
+    if (!d || !out) return 1;
+    orc_scene* s = new orc_scene();
+    s->prims.assign(d->prims, d->prims + d->n_prims);
+    if (d->n_transforms) s->xforms.assign(d->transforms, d->transforms + d->n_transforms);
+    if (d->n_materials) s->mats.assign(d->materials, d->materials + d->n_materials);
+    if (d->n_textures) s->texs.assign(d->textures, d->textures + d->n_textures);
+    if (d->n_perlin) s->perlin.assign(d->perlin, d->perlin + d->n_perlin);
+    for (int i = 0; i < d->n_images; i++) {
+        rtw_image im = d->images[i];
+        s->image_data.emplace_back(im.rgba, im.rgba + (size_t)im.width * im.height * 4);
+        s->images.push_back(im);
+    }
+    for (int i = 0; i < d->n_images; i++) s->images[i].rgba = s->image_data[i].data();
+    if (d->n_lights) s->lights.assign(d->lights, d->lights + d->n_lights);
+    s->has_light_rect = d->has_light_rect;
+    s->light_rect = d->light_rect;
+    s->cam = d->camera;
+    s->sky_light = d->sky_light;
+    *out = s;
+    return 0;
+}
+extern "C" void orc_scene_free(orc_scene* s) { delete s; }
+
+// ============================================================================
+// Per-ray data (lib/raydata.cuh:60-80) and hit record (raydata.cuh:117-124)
+// ============================================================================
+enum ScatterEvent { Ray_Miss, Ray_Hit, Ray_Finish, Ray_Cancel };  // raydata.cuh:15-21
+
+struct PerRayData {
+    V3 attenuation;
+    V3 scattered_origin;
+    V3 scattered_direction;
+    V3 emitted;
+    V3 radiance;
+    float distance;
+    V3 hit_normal;
+    ScatterEvent scatterEvent;
+    float pdf;
+    V3 lightDirection;
+    int materialType;
+    float scattered_pdf;
+    float gatherTime;
+    uint32_t seed;
+    int depth;
+    bool is_specular;
+};
+
+struct HitRecord {
+    V3 point;
+    V3 normal;
+    float distance;
+    float u, v;
+};
+
+struct Ray {
+    V3 o, d;
+    float tmin, tmax;
+    float time;         // ray time (motion key interpolation)
+    float gather_time;  // PerRayData::gatherTime
+    uint32_t seed;      // path seed at ray start (Q23 normalisation)
+};
+
+struct Counters {
+    uint64_t paths = 0, rays_closest = 0, rays_shadow = 0, nodes = 0, prims = 0, vertices = 0;
+    void add_to(orc_counters* o) const {
+        if (!o) return;
+        o->paths += paths; o->rays_closest += rays_closest; o->rays_shadow += rays_shadow;
+        o->nodes_visited += nodes; o->prims_tested += prims; o->vertices_shaded += vertices;
+        o->shadow_enqueued += rays_shadow;
+    }
+};
+
+// ============================================================================
+// Intersection programs → "candidate" functions.
+// OptiX semantics supplied here: object-space ray = W2O * world ray,
+// optixReportIntersection accepts iff tmin <= t <= tmax; closest hit = the
+// lexicographic minimum of (t, primitive index) over all accepted candidates,
+// which makes the result independent of traversal order.
+// ============================================================================
+
+// geometry/sphere.cu:24-32
+static inline void get_sphere_uv(V3 p, float& u, float& v) {
+    float phi = atan2f(p.z, p.x);
+    float theta = asinf(p.y);
+    u = 1 - (phi + kPi) / (2.f * kPi);
+    v = (theta + kPiO2) / kPi;
+}
+
+// Motion-matrix interpolation of the moving sphere's instance child
+// (geometry/ioMovingSphere.h:162-182): translation key0 = c0, key1 = c1,
+// timeBegin 0, timeEnd 1, clamped; M(t) = (1-f)*key0 + f*key1 (OptiX runtime
+// semantics, restated; unpinned).
+static inline V3 motion_translation(const rtw_prim& p, float ray_time) {
+    float f = ray_time;  // (t - 0) / (1 - 0)
+    if (f < 0.f) f = 0.f;
+    if (f > 1.f) f = 1.f;
+    V3 c0 = v3(p.v[0], p.v[1], p.v[2]), c1 = v3(p.v[4], p.v[5], p.v[6]);
+    return c0 * (1.0f - f) + c1 * f;
+}
+// geometry/movingSphere.cu:33-39
+static inline V3 moving_center(const rtw_prim& p, float time) {
+    V3 c0 = v3(p.v[0], p.v[1], p.v[2]), c1 = v3(p.v[4], p.v[5], p.v[6]);
+    float t0 = p.v[7], t1 = p.v[8];
+    if (t0 == t1) return c0;
+    return c0 + ((time - t0) / (t1 - t0)) * (c1 - c0);
+}
+
+// Object-space ray for primitive p.
+static inline void object_ray(const orc_scene& s, const rtw_prim& p, const Ray& r, V3& o, V3& d) {
+    if (p.type == RTW_PRIM_MOVING_SPHERE) {  // Q24: motion transform, literal
+        o = r.o - motion_translation(p, r.time);
+        d = r.d;
+    } else if (p.transform >= 0) {
+        const float* m = s.xforms[p.transform].w2o;
+        o = xform_point(m, r.o);
+        d = xform_vector(m, r.d);
+    } else {
+        o = r.o;
+        d = r.d;
+    }
+}
+
+// Free-flight uniform for constant media.  Q23 NORMALISED: the reference draws
+// from thePrd->seed inside the intersection program (traversal-order dependent);
+// here the state is tea<4>(path seed at ray start, primitive index) and the path
+// seed is not mutated.  Generators kept: randf for the box (volumeBox.cu:79),
+// rnd for the sphere (volumeSphere.cu:93).
+static inline uint32_t medium_state(uint32_t ray_seed, int prim) { return tea_n(4, ray_seed, (uint32_t)prim); }
+
+// geometry/volumeBox.cu:29-52
+static inline bool hit_boundary_box(V3 direction, V3 origin, V3 boxMin, V3 boxMax, float tMin, float tMax, float& rec) {
+    V3 t0 = (boxMin - origin) / direction;
+    V3 t1 = (boxMax - origin) / direction;
+    float temp1 = fmaxf3(vmin(t0, t1));
+    float temp2 = fminf3(vmax(t0, t1));
+    if (temp1 > temp2) return false;
+    if (temp1 < tMax && temp1 > tMin) { rec = temp1; return true; }
+    if (temp2 < tMax && temp2 > tMin) { rec = temp2; return true; }
+    return false;
+}
+// geometry/volumeSphere.cu:37-61
+static inline bool hit_boundary_sphere(V3 direction, V3 origin, V3 center, float radius, float tmin, float tmax, float& rec) {
+    V3 oc = origin - center;
+    float a = dot(direction, direction);
+    float b = dot(oc, direction);
+    float c = dot(oc, oc) - radius * radius;
+    float discriminant = b * b - a * c;
+    if (discriminant < 0.f) return false;
+    float t = (-b - sqrtf(discriminant)) / a;
+    if (t < tmax && t > tmin) { rec = t; return true; }
+    t = (-b + sqrtf(discriminant)) / a;
+    if (t < tmax && t > tmin) { rec = t; return true; }
+    return false;
+}
+
+// Returns true and the accepted hit distance if primitive `pi` reports an
+// intersection for ray r that optixReportIntersection would accept.
+static bool candidate(const orc_scene& s, int pi, const Ray& r, float& t_out) {
+    const rtw_prim& p = s.prims[pi];
+    V3 o, d;
+    object_ray(s, p, r, o, d);
+    const float tmin = r.tmin, tmax = r.tmax;
+    switch (p.type) {
+    case RTW_PRIM_SPHERE:
+    case RTW_PRIM_MOVING_SPHERE: {
+        // geometry/sphere.cu:48-120, geometry/movingSphere.cu:61-135
+        V3 c = (p.type == RTW_PRIM_SPHERE) ? v3(p.v[0], p.v[1], p.v[2]) : moving_center(p, r.gather_time);
+        float radius = p.v[3];
+        V3 oc = o - c;
+        float a = dot(d, d);
+        float b = dot(oc, d);
+        float cc = dot(oc, oc) - radius * radius;
+        float discriminant = b * b - a * cc;
+        if (discriminant < 0.0f) return false;
+        float t = (-b - sqrtf(discriminant)) / a;
+        if (t < tmax && t > tmin) { t_out = t; return true; }
+        t = (-b + sqrtf(discriminant)) / a;
+        if (t < tmax && t > tmin) { t_out = t; return true; }
+        return false;
+    }
+    case RTW_PRIM_RECT_X:
+    case RTW_PRIM_RECT_Y:
+    case RTW_PRIM_RECT_Z: {
+        // shaders/aarectx.cu:8-49, aarecty.cu:8-50, aarectz.cu:9-51
+        const float a0 = p.v[0], a1 = p.v[1], b0 = p.v[2], b1 = p.v[3], k = p.v[4];
+        float t, a, b;
+        if (p.type == RTW_PRIM_RECT_X) {
+            t = (k - o.x) / d.x;
+            if (t > tmax || t < tmin) return false;
+            a = o.y + t * d.y;
+            b = o.z + t * d.z;
+        } else if (p.type == RTW_PRIM_RECT_Y) {
+            t = (k - o.y) / d.y;
+            if (t > tmax || t < tmin) return false;
+            a = o.x + t * d.x;
+            b = o.z + t * d.z;
+        } else {
+            t = (k - o.z) / d.z;
+            if (t > tmax || t < tmin) return false;
+            a = o.x + t * d.x;
+            b = o.y + t * d.y;
+        }
+        if (a < a0 || a > a1 || b < b0 || b > b1) return false;
+        if (!(t >= tmin && t <= tmax)) return false;  // optixReportIntersection (rejects NaN)
+        t_out = t;
+        return true;
+    }
+    case RTW_PRIM_VOLUME_BOX: {
+        // geometry/volumeBox.cu:55-113; EPSILON is `constexpr int` == 0 (Q23)
+        V3 bmin = v3(p.v[0], p.v[1], p.v[2]), bmax = v3(p.v[3], p.v[4], p.v[5]);
+        float density = p.v[6];
+        float hitt1, hitt2;
+        if (!hit_boundary_box(d, o, bmin, bmax, -FLT_MAX, FLT_MAX, hitt1)) return false;
+        if (!hit_boundary_box(d, o, bmin, bmax, hitt1 + 0, FLT_MAX, hitt2)) return false;
+        if (hitt1 < tmin) hitt1 = tmin;
+        if (hitt2 > tmax) hitt2 = tmax;
+        if (hitt1 >= hitt2) return false;
+        if (hitt1 < 0.f) hitt1 = 0.f;
+        // distanceInsideBoundary computed but never compared (Q23)
+        uint32_t st = medium_state(r.seed, pi);
+        float hitDistance = -(1.f / density) * logf(randf(st));
+        float hitt = hitt1 + (hitDistance / length(d));
+        if (!(hitt >= tmin && hitt <= tmax)) return false;
+        t_out = hitt;
+        return true;
+    }
+    case RTW_PRIM_VOLUME_SPHERE: {
+        // geometry/volumeSphere.cu:67-127
+        V3 c = v3(p.v[0], p.v[1], p.v[2]);
+        float radius = p.v[3], density = p.v[4];
+        float hitt1, hitt2;
+        if (!hit_boundary_sphere(d, o, c, radius, -FLT_MAX, FLT_MAX, hitt1)) return false;
+        if (!hit_boundary_sphere(d, o, c, radius, hitt1 + 0, FLT_MAX, hitt2)) return false;
+        if (hitt1 < tmin) hitt1 = tmin;
+        if (hitt2 > tmax) hitt2 = tmax;
+        if (hitt1 >= hitt2) return false;
+        if (hitt1 < 0.f) hitt1 = 0.f;
+        uint32_t st = medium_state(r.seed, pi);
+        float hitDistance = -(1.f / density) * logf(rnd(st));
+        float hitt = hitt1 + (hitDistance / length(d));
+        if (!(hitt >= tmin && hitt <= tmax)) return false;
+        t_out = hitt;
+        return true;
+    }
+    default:
+        return false;
+    }
+}
+
+// Attributes the winning intersection program reports (normal, uv, point).
+static void hit_attributes(const orc_scene& s, int pi, const Ray& r, float t, HitRecord& h) {
+    const rtw_prim& p = s.prims[pi];
+    V3 o, d;
+    object_ray(s, p, r, o, d);
+    const float* o2w = nullptr;
+    const float* w2o = nullptr;
+    if (p.type != RTW_PRIM_MOVING_SPHERE && p.transform >= 0) {
+        o2w = s.xforms[p.transform].o2w;
+        w2o = s.xforms[p.transform].w2o;
+    }
+    V3 pobj = o + t * d;
+    V3 point;
+    if (p.type == RTW_PRIM_MOVING_SPHERE) point = pobj + motion_translation(p, r.time);
+    else point = o2w ? xform_point(o2w, pobj) : pobj;
+    h.point = point;
+    h.distance = t;
+    switch (p.type) {
+    case RTW_PRIM_SPHERE:
+    case RTW_PRIM_MOVING_SPHERE: {
+        // Q21: world-space point minus OBJECT-space centre, not normalised.
+        V3 c = (p.type == RTW_PRIM_SPHERE) ? v3(p.v[0], p.v[1], p.v[2]) : moving_center(p, r.gather_time);
+        V3 n = (point - c) / p.v[3];
+        if (w2o) n = xform_normal(w2o, n);
+        h.normal = n;
+        get_sphere_uv(n, h.u, h.v);
+        break;
+    }
+    case RTW_PRIM_RECT_X:
+    case RTW_PRIM_RECT_Y:
+    case RTW_PRIM_RECT_Z: {
+        const float a0 = p.v[0], a1 = p.v[1], b0 = p.v[2], b1 = p.v[3];
+        float a, b;
+        V3 n;
+        if (p.type == RTW_PRIM_RECT_X) { a = o.y + t * d.y; b = o.z + t * d.z; n = v3(1.f, 0.f, 0.f); }
+        else if (p.type == RTW_PRIM_RECT_Y) { a = o.x + t * d.x; b = o.z + t * d.z; n = v3(0.f, 1.f, 0.f); }
+        else { a = o.x + t * d.x; b = o.y + t * d.y; n = v3(0.f, 0.f, 1.f); }
+        if (p.flip) n = -n;
+        if (w2o) n = xform_normal(w2o, n);
+        h.normal = normalize(n);
+        h.u = (a - a0) / (a1 - a0);
+        h.v = (b - b0) / (b1 - b0);
+        break;
+    }
+    default: {  // volumes: normal (1,0,0), uv 0 (volumeBox.cu:88-93, volumeSphere.cu:99-105)
+        V3 n = v3(1.f, 0.f, 0.f);
+        if (w2o) n = xform_normal(w2o, n);
+        h.normal = normalize(n);
+        h.u = 0.f;
+        h.v = 0.f;
+        break;
+    }
+    }
+}
+
+// ============================================================================
+// Host-mirror LBVH (same algorithm as the device builder; DESIGN.md "LBVH")
+// ============================================================================
+static Aabb prim_aabb(const orc_scene& s, int pi) {
+    const rtw_prim& p = s.prims[pi];
+    Aabb b;
+    switch (p.type) {
+    case RTW_PRIM_SPHERE: {  // geometry/ioSphere.h:25-34
+        V3 c = v3(p.v[0], p.v[1], p.v[2]);
+        b.mn = c - p.v[3];
+        b.mx = c + p.v[3];
+        break;
+    }
+    case RTW_PRIM_MOVING_SPHERE: {  // geometry/ioMovingSphere.h:46-72 + motion keys (Q24)
+        V3 c0 = v3(p.v[0], p.v[1], p.v[2]), c1 = v3(p.v[4], p.v[5], p.v[6]);
+        float r = p.v[3];
+        V3 lo = vmin(c0 - r, c1 - r), hi = vmax(c0 + r, c1 + r);
+        b.mn = vmin(lo + c0, lo + c1);
+        b.mx = vmax(hi + c0, hi + c1);
+        return b;  // no instance transform on moving spheres
+    }
+    case RTW_PRIM_RECT_X:  // geometry/ioAARect.h:128-154
+        b.mn = v3(p.v[4] - 0.0001f, p.v[0], p.v[2]);
+        b.mx = v3(p.v[4] + 0.0001f, p.v[1], p.v[3]);
+        break;
+    case RTW_PRIM_RECT_Y:
+        b.mn = v3(p.v[0], p.v[4] - 0.0001f, p.v[2]);
+        b.mx = v3(p.v[1], p.v[4] + 0.0001f, p.v[3]);
+        break;
+    case RTW_PRIM_RECT_Z:
+        b.mn = v3(p.v[0], p.v[2], p.v[4] - 0.0001f);
+        b.mx = v3(p.v[1], p.v[3], p.v[4] + 0.0001f);
+        break;
+    case RTW_PRIM_VOLUME_BOX:  // geometry/ioVolumeBox.h:76-84
+        b.mn = v3(p.v[0], p.v[1], p.v[2]) - 0.0001f;
+        b.mx = v3(p.v[3], p.v[4], p.v[5]) + 0.0001f;
+        break;
+    default: {  // geometry/ioVolumeSphere.h:76-82
+        V3 c = v3(p.v[0], p.v[1], p.v[2]);
+        float r = fabsf(p.v[3]);
+        b.mn = c - r;
+        b.mx = c + r;
+        break;
+    }
+    }
+    if (p.transform >= 0) {  // instance transform: box of the 8 transformed corners
+        const float* m = s.xforms[p.transform].o2w;
+        Aabb w;
+        w.mn = v3(FLT_MAX);
+        w.mx = v3(-FLT_MAX);
+        for (int i = 0; i < 8; i++) {
+            V3 c = v3((i & 1) ? b.mx.x : b.mn.x, (i & 2) ? b.mx.y : b.mn.y, (i & 4) ? b.mx.z : b.mn.z);
+            V3 q = xform_point(m, c);
+            w.mn = vmin(w.mn, q);
+            w.mx = vmax(w.mx, q);
+        }
+        b = w;
+    }
+    return b;
+}
+
+// conservative pad: 2^-21 of the largest |coordinate| (DESIGN.md "LBVH")
+static Aabb pad_aabb(Aabb b) {
+    float m = fmaxf(fmaxf(fmaxf(fabsf(b.mn.x), fabsf(b.mn.y)), fabsf(b.mn.z)),
+                    fmaxf(fmaxf(fabsf(b.mx.x), fabsf(b.mx.y)), fabsf(b.mx.z)));
+    float pad = m * 4.76837158203125e-7f;
+    b.mn = b.mn - pad;
+    b.mx = b.mx + pad;
+    return b;
+}
+
+static inline uint64_t expand21(uint32_t v) {  // spread 21 bits to every third bit
+    uint64_t x = v & 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+static inline uint32_t quant21(float c, float lo, float ext) {
+    float n = (ext > 0.f) ? (c - lo) / ext : 0.f;
+    float q = n * 2097152.0f;
+    if (!(q >= 0.f)) q = 0.f;
+    if (q > 2097151.0f) q = 2097151.0f;
+    return (uint32_t)q;
+}
+static inline uint64_t morton63(V3 c, V3 lo, V3 ext) {
+    return (expand21(quant21(c.x, lo.x, ext.x)) << 2) | (expand21(quant21(c.y, lo.y, ext.y)) << 1) |
+           expand21(quant21(c.z, lo.z, ext.z));
+}
+static inline int clz64(uint64_t x) { return x ? __builtin_clzll(x) : 64; }
+static inline int clz32(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+
+extern "C" void orc_prim_aabbs(const orc_scene* s, float* out) {
+    for (size_t i = 0; i < s->prims.size(); i++) {
+        Aabb b = pad_aabb(prim_aabb(*s, (int)i));
+        out[i * 6 + 0] = b.mn.x; out[i * 6 + 1] = b.mn.y; out[i * 6 + 2] = b.mn.z;
+        out[i * 6 + 3] = b.mx.x; out[i * 6 + 4] = b.mx.y; out[i * 6 + 5] = b.mx.z;
+    }
+}
+
+extern "C" int orc_bvh_build(orc_scene* s) {
+    const int n = (int)s->prims.size();
+    if (n <= 0) return 1;
+    std::vector<Aabb> boxes(n);
+    Aabb sb;
+    sb.mn = v3(FLT_MAX);
+    sb.mx = v3(-FLT_MAX);
+    for (int i = 0; i < n; i++) {
+        boxes[i] = pad_aabb(prim_aabb(*s, i));
+        sb.mn = vmin(sb.mn, boxes[i].mn);
+        sb.mx = vmax(sb.mx, boxes[i].mx);
+    }
+    s->scene_box = sb;
+    V3 ext = sb.mx - sb.mn;
+    std::vector<std::pair<uint64_t, int>> keys(n);
+    for (int i = 0; i < n; i++) {
+        V3 c = (boxes[i].mn + boxes[i].mx) * 0.5f;
+        keys[i] = {morton63(c, sb.mn, ext), i};
+    }
+    std::stable_sort(keys.begin(), keys.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    s->morton.resize(n);
+    s->leaf_prim.resize(n);
+    for (int i = 0; i < n; i++) { s->morton[i] = keys[i].first; s->leaf_prim[i] = keys[i].second; }
+    const int ni = std::max(n - 1, 1);
+    s->nodes.assign(ni, BvhNode{});
+    std::vector<int> leaf_parent(n, -1);
+    const uint64_t* k = s->morton.data();
+    auto delta = [&](int i, int j) -> int {
+        if (j < 0 || j >= n) return -1;
+        if (k[i] == k[j]) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
+        return clz64(k[i] ^ k[j]);
+    };
+    if (n == 1) {
+        BvhNode& nd = s->nodes[0];
+        nd.left = ~0; nd.right = ~0; nd.parent = -1;
+        nd.lmin = boxes[s->leaf_prim[0]].mn; nd.lmax = boxes[s->leaf_prim[0]].mx;
+        nd.rmin = v3(FLT_MAX); nd.rmax = v3(-FLT_MAX);  // empty: never entered
+        s->bvh_built = true;
+        return 0;
+    }
+    s->nodes[0].parent = -1;
+    for (int i = 0; i < n - 1; i++) {  // Karras 2012
+        int d = (delta(i, i + 1) - delta(i, i - 1)) >= 0 ? 1 : -1;
+        int dmin = delta(i, i - d);
+        int lmax = 2;
+        while (delta(i, i + lmax * d) > dmin) lmax *= 2;
+        int l = 0;
+        for (int t = lmax / 2; t >= 1; t /= 2)
+            if (delta(i, i + (l + t) * d) > dmin) l += t;
+        int j = i + l * d;
+        int dnode = delta(i, j);
+        int sp = 0;
+        int t = l;
+        do {
+            t = (t + 1) >> 1;
+            if (delta(i, i + (sp + t) * d) > dnode) sp += t;
+        } while (t > 1);
+        int gamma = i + sp * d + std::min(d, 0);
+        int lo = std::min(i, j), hi = std::max(i, j);
+        BvhNode& nd = s->nodes[i];
+        if (lo == gamma) { nd.left = ~gamma; leaf_parent[gamma] = i; }
+        else { nd.left = gamma; s->nodes[gamma].parent = i; }
+        if (hi == gamma + 1) { nd.right = ~(gamma + 1); leaf_parent[gamma + 1] = i; }
+        else { nd.right = gamma + 1; s->nodes[gamma + 1].parent = i; }
+    }
+    // bottom-up refit
+    std::vector<int> visits(ni, 0);
+    for (int leaf = 0; leaf < n; leaf++) {
+        int cur = leaf_parent[leaf];
+        while (cur >= 0) {
+            if (visits[cur]++ == 0) break;  // first arrival stops, second computes
+            BvhNode& nd = s->nodes[cur];
+            auto child_box = [&](int ref) -> Aabb {
+                if (ref < 0) return boxes[s->leaf_prim[~ref]];
+                const BvhNode& c = s->nodes[ref];
+                return Aabb{vmin(c.lmin, c.rmin), vmax(c.lmax, c.rmax)};
+            };
+            Aabb l = child_box(nd.left), r = child_box(nd.right);
+            nd.lmin = l.mn; nd.lmax = l.mx; nd.rmin = r.mn; nd.rmax = r.mx;
+            cur = nd.parent;
+        }
+    }
+    s->bvh_built = true;
+    return 0;
+}
+
+extern "C" int orc_bvh_info(const orc_scene* s, rtw_bvh_info* info) {
+    if (!s->bvh_built) return 1;
+    info->n_leaves = (int)s->prims.size();
+    info->n_internal = (int)s->nodes.size();
+    info->root = 0;
+    info->n_top = 0;
+    info->scene_min[0] = s->scene_box.mn.x; info->scene_min[1] = s->scene_box.mn.y; info->scene_min[2] = s->scene_box.mn.z;
+    info->scene_max[0] = s->scene_box.mx.x; info->scene_max[1] = s->scene_box.mx.y; info->scene_max[2] = s->scene_box.mx.z;
+    return 0;
+}
+
+extern "C" int orc_bvh_download(const orc_scene* s, uint64_t* morton, int32_t* leaf_prim, int32_t* left,
+                                int32_t* right, float* bounds) {
+    if (!s->bvh_built) return 1;
+    const int n = (int)s->prims.size(), ni = (int)s->nodes.size();
+    if (morton) memcpy(morton, s->morton.data(), sizeof(uint64_t) * n);
+    if (leaf_prim) memcpy(leaf_prim, s->leaf_prim.data(), sizeof(int32_t) * n);
+    for (int i = 0; i < ni; i++) {
+        const BvhNode& nd = s->nodes[i];
+        if (left) left[i] = nd.left;
+        if (right) right[i] = nd.right;
+        if (bounds) {
+            float* b = bounds + (size_t)i * 12;
+            b[0] = nd.lmin.x; b[1] = nd.lmin.y; b[2] = nd.lmin.z; b[3] = nd.lmax.x; b[4] = nd.lmax.y; b[5] = nd.lmax.z;
+            b[6] = nd.rmin.x; b[7] = nd.rmin.y; b[8] = nd.rmin.z; b[9] = nd.rmax.x; b[10] = nd.rmax.y; b[11] = nd.rmax.z;
+        }
+    }
+    return 0;
+}
+
+// conservative slab test against [tmin, tlimit]
+static inline bool slab(V3 mn, V3 mx, V3 o, V3 inv, float tmin, float tlimit, float& tnear) {
+    float tx0 = (mn.x - o.x) * inv.x, tx1 = (mx.x - o.x) * inv.x;
+    float ty0 = (mn.y - o.y) * inv.y, ty1 = (mx.y - o.y) * inv.y;
+    float tz0 = (mn.z - o.z) * inv.z, tz1 = (mx.z - o.z) * inv.z;
+    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), tmin));
+    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), tlimit));
+    tnear = tn;
+    return tn <= tf * 1.0000004f;
+}
+
+// ============================================================================
+// Traversal: closest hit / any hit
+// ============================================================================
+static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_best, int& prim_best, Counters& c) {
+    c.rays_closest++;
+    t_best = 0.f;
+    prim_best = -1;
+    bool found = false;
+    auto consider = [&](int pi) {
+        float t;
+        c.prims++;
+        if (candidate(s, pi, r, t)) {
+            if (!found || t < t_best || (t == t_best && pi < prim_best)) {
+                found = true;
+                t_best = t;
+                prim_best = pi;
+            }
+        }
+    };
+    if (mode == 0 || !s.bvh_built) {
+        for (int i = 0; i < (int)s.prims.size(); i++) consider(i);
+        return found;
+    }
+    V3 inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    int stack[128];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+        int ni = stack[--sp];
+        const BvhNode& nd = s.nodes[ni];
+        c.nodes++;
+        float limit = found ? t_best : r.tmax;
+        float tl, tr;
+        bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, limit, tl);
+        bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, limit, tr);
+        // volumes report hits beyond their exit point, but never before the box entry;
+        // NaN-direction rays (0 * inf) fall through to a conservative visit.
+        if (tl != tl) hl = true;
+        if (tr != tr) hr = true;
+        int refs[2] = {nd.left, nd.right};
+        bool hits[2] = {hl, hr};
+        for (int k = 0; k < 2; k++) {
+            if (!hits[k]) continue;
+            if (refs[k] < 0) consider(s.leaf_prim[~refs[k]]);
+            else if (sp < 128) stack[sp++] = refs[k];
+        }
+    }
+    return found;
+}
+
+static bool trace_any(const orc_scene& s, const Ray& r, int mode, Counters& c) {
+    c.rays_shadow++;
+    if (mode == 0 || !s.bvh_built) {
+        for (int i = 0; i < (int)s.prims.size(); i++) {
+            float t;
+            c.prims++;
+            if (candidate(s, i, r, t)) return true;
+        }
+        return false;
+    }
+    V3 inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    int stack[128];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+        int ni = stack[--sp];
+        const BvhNode& nd = s.nodes[ni];
+        c.nodes++;
+        float tl, tr;
+        bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, r.tmax, tl);
+        bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, r.tmax, tr);
+        if (tl != tl) hl = true;
+        if (tr != tr) hr = true;
+        int refs[2] = {nd.left, nd.right};
+        bool hits[2] = {hl, hr};
+        for (int k = 0; k < 2; k++) {
+            if (!hits[k]) continue;
+            if (refs[k] < 0) {
+                float t;
+                c.prims++;
+                if (candidate(s, s.leaf_prim[~refs[k]], r, t)) return true;
+            } else if (sp < 128) stack[sp++] = refs[k];
+        }
+    }
+    return false;
+}
+
+static inline Ray from_abi(const rtw_ray& a) {
+    Ray r;
+    r.o = v3(a.origin); r.d = v3(a.dir);
+    r.tmin = a.tmin; r.tmax = a.tmax; r.time = a.time; r.gather_time = a.gather_time; r.seed = a.seed;
+    return r;
+}
+
+extern "C" void orc_trace_closest(const orc_scene* s, const rtw_ray* rays, int n, rtw_hit* hits, int mode,
+                                  orc_counters* counters) {
+    Counters c;
+    for (int i = 0; i < n; i++) {
+        Ray r = from_abi(rays[i]);
+        float t; int p;
+        bool f = trace_closest(*s, r, mode, t, p, c);
+        hits[i].t = f ? t : 0.f;
+        hits[i].prim = f ? p : -1;
+    }
+    c.add_to(counters);
+}
+extern "C" void orc_trace_any(const orc_scene* s, const rtw_ray* rays, int n, int32_t* occ, int mode,
+                              orc_counters* counters) {
+    Counters c;
+    for (int i = 0; i < n; i++) occ[i] = trace_any(*s, from_abi(rays[i]), mode, c) ? 1 : 0;
+    c.add_to(counters);
+}
+
+// ============================================================================
+// Sampling helpers (lib/sampling.cuh, lib/onb.cuh)
+// ============================================================================
+// lib/sampling.cuh:15-22
+static inline V3 random_in_unit_disk(uint32_t& seed) {
+    float a = rnd(seed) * 2.0f * kPi;
+    V3 xy = v3(sinf(a), cosf(a), 0);
+    xy *= sqrtf(rnd(seed));
+    return xy;
+}
+// lib/sampling.cuh:25-34; the three draws are sequenced x, y, z (SURVEY §7b caveat)
+static inline V3 randomInUnitSphere(uint32_t& seed) {
+    V3 p;
+    do {
+        float x = rnd(seed);
+        float y = rnd(seed);
+        float z = rnd(seed);
+        p = 2.0f * v3(x, y, z) - v3(1.0f, 1.0f, 1.0f);
+    } while (dot(p, p) >= 1.0f);
+    return p;
+}
+// lib/sampling.cuh:49-60 (Q10: the factor 2 is literal)
+static inline V3 randomCosineDirection(uint32_t& seed) {
+    float r1 = rnd(seed);
+    float r2 = rnd(seed);
+    float phi = 2.f * kPi * r1;
+    float x = cosf(phi) * 2 * sqrtf(r2);
+    float y = sinf(phi) * 2 * sqrtf(r2);
+    float z = sqrtf(1 - r2);
+    return v3(x, y, z);
+}
+// lib/onb.cuh:9-35
+struct Onb {
+    V3 u, v, w;
+    void buildFromW(V3 n) {
+        w = normalize(n);
+        V3 a;
+        if ((w.x > 0.9f) || (w.x < -0.9f)) a = v3(0.f, 1.f, 0.f);
+        else a = v3(1.f, 0.f, 0.f);
+        v = normalize(cross(w, a));
+        u = cross(w, v);
+    }
+    V3 local(V3 a) const { return a.x * u + a.y * v + a.z * w; }
+};
+
+// ============================================================================
+// Textures (texture/*.cu)
+// ============================================================================
+// texture/noiseTexture.cu:19-37
+static inline float perlin_interp(V3 c[2][2][2], float u, float v, float w) {
+    float uu = u * u * (3 - 2 * u);
+    float vv = v * v * (3 - 2 * v);
+    float ww = w * w * (3 - 2 * w);
+    float accum = 0;
+    for (int i = 0; i < 2; i++)
+        for (int j = 0; j < 2; j++)
+            for (int k = 0; k < 2; k++) {
+                V3 weight_v = v3(u - i, v - j, w - k);
+                accum += (i * uu + (1 - i) * (1 - uu)) * (j * vv + (1 - j) * (1 - vv)) *
+                         (k * ww + (1 - k) * (1 - ww)) * dot(c[i][j][k], weight_v);
+            }
+    return accum;
+}
+// texture/noiseTexture.cu:39-55
+static inline float perlin_noise(const rtw_perlin& t, V3 p) {
+    float u = p.x - floorf(p.x);
+    float v = p.y - floorf(p.y);
+    float w = p.z - floorf(p.z);
+    int i = (int)floorf(p.x);
+    int j = (int)floorf(p.y);
+    int k = (int)floorf(p.z);
+    V3 c[2][2][2];
+    for (int di = 0; di < 2; di++)
+        for (int dj = 0; dj < 2; dj++)
+            for (int dk = 0; dk < 2; dk++) {
+                int idx = t.perm_x[(i + di) & 255] ^ t.perm_y[(j + dj) & 255] ^ t.perm_z[(k + dk) & 255];
+                c[di][dj][dk] = v3(t.ranvec[idx]);
+            }
+    return perlin_interp(c, u, v, w);
+}
+// texture/noiseTexture.cu:57-70
+static inline float perlin_turb(const rtw_perlin& t, V3 p) {
+    float accum = 0;
+    V3 temp_p = p;
+    float weight = 1.0;
+    for (int i = 0; i < 7; i++) {
+        accum += weight * perlin_noise(t, temp_p);
+        weight *= 0.5f;
+        temp_p *= 2.f;
+    }
+    return fabsf(accum);
+}
+
+// Image lookup: the reference uses the hardware unit (tex2D, normalised coords,
+// clamp, linear; texture/imageTexture.cu:15, texture/ioTexture.h:284-300).  Q20
+// NORMALISED to a manual fp32 bilinear on the RGBA8 texels (SURVEY §7 hard parts):
+// x = u*W - 0.5, i = floor(x), f = x - i, indices clamped, NaN → 0.
+static inline V3 image_lookup(const rtw_image& im, float u, float v) {
+    float x = u * (float)im.width - 0.5f;
+    float y = v * (float)im.height - 0.5f;
+    if (!(x == x)) x = 0.f;
+    if (!(y == y)) y = 0.f;
+    float fx0 = floorf(x), fy0 = floorf(y);
+    float fx = x - fx0, fy = y - fy0;
+    // clamp in float first (|x| may be huge), then to int
+    float wmax = (float)(im.width - 1), hmax = (float)(im.height - 1);
+    int x0 = (int)fminf(fmaxf(fx0, 0.f), wmax), x1 = (int)fminf(fmaxf(fx0 + 1.f, 0.f), wmax);
+    int y0 = (int)fminf(fmaxf(fy0, 0.f), hmax), y1 = (int)fminf(fmaxf(fy0 + 1.f, 0.f), hmax);
+    auto texel = [&](int xi, int yi) -> V3 {
+        const uint8_t* p = im.rgba + ((size_t)yi * im.width + xi) * 4;
+        return v3((float)p[0] / 255.0f, (float)p[1] / 255.0f, (float)p[2] / 255.0f);
+    };
+    V3 t00 = texel(x0, y0), t10 = texel(x1, y0), t01 = texel(x0, y1), t11 = texel(x1, y1);
+    V3 r0 = t00 * (1.0f - fx) + t10 * fx;
+    V3 r1 = t01 * (1.0f - fx) + t11 * fx;
+    return r0 * (1.0f - fy) + r1 * fy;
+}
+
+static V3 texture_eval(const orc_scene& s, int ti, float u, float v, V3 p, int depth = 0) {
+    if (ti < 0 || ti >= (int)s.texs.size() || depth > 8) return v3(0.f);
+    const rtw_texture& t = s.texs[ti];
+    switch (t.type) {
+    case RTW_TEX_CONSTANT:  // texture/constantTexture.cu:5-10
+        return v3(t.color);
+    case RTW_TEX_CHECKER: {  // texture/checkeredTexture.cu:9-20 (Q18: children dispatched correctly)
+        float sines = sinf(10.f * p.x) * sinf(10.f - p.y) * sinf(10.f * p.z);
+        if (sines < 0) return texture_eval(s, t.odd, u, v, p, depth + 1);
+        return texture_eval(s, t.even, u, v, p, depth + 1);
+    }
+    case RTW_TEX_IMAGE:  // texture/imageTexture.cu:10-16
+        return image_lookup(s.images[t.image], u, v);
+    case RTW_TEX_NOISE: {  // texture/noiseTexture.cu:72-83
+        const rtw_perlin& tab = s.perlin[t.perlin];
+        return v3(1.f) * 0.5f * (1.0f + sinf(t.scale * p.z + 5.f * perlin_turb(tab, t.scale * p)));
+    }
+    default:  // texture/nullTexture.cu:7-12
+        return v3(0.f, 0.f, 0.f);
+    }
+}
+
+extern "C" void orc_texture_eval(const orc_scene* s, int texture, float u, float v, const float* p, float* out) {
+    V3 c = texture_eval(*s, texture, u, v, v3(p));
+    out[0] = c.x; out[1] = c.y; out[2] = c.z;
+}
+
+// ============================================================================
+// Materials (material/*.cu) — direct callables
+// ============================================================================
+// material/lambertianMaterial.cu:29-38
+static inline float lambert_scatteringPdf(const HitRecord& h, const PerRayData& prd) {
+    float cosine = dot(h.normal, normalize(prd.scattered_direction));
+    if (cosine < 0.f) return 0.f;
+    return cosine / kPi;
+}
+// material/lambertianMaterial.cu:41-71
+static void mat_lambertian(const orc_scene& s, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {
+    (void)direction;
+    Onb uvw;
+    uvw.buildFromW(h.normal);
+    V3 w = randomCosineDirection(prd.seed);
+    prd.pdf = w.z * kInvPi;
+    V3 scatterDirection = normalize(uvw.local(w));
+    prd.emitted = v3(0.f);
+    prd.is_specular = false;
+    prd.materialType = RTW_MAT_LAMBERTIAN;
+    prd.scatterEvent = Ray_Hit;
+    prd.hit_normal = h.normal;
+    prd.scattered_origin = h.point;
+    prd.scattered_direction = scatterDirection;
+    prd.scattered_pdf = lambert_scatteringPdf(h, prd);
+    if (prd.scattered_pdf <= 0 || prd.pdf <= 0) {
+        prd.scatterEvent = Ray_Cancel;
+        return;
+    }
+    prd.attenuation = texture_eval(s, m.texture, h.u, h.v, h.point);
+}
+// material/metalMaterial.cu:32-64
+static void mat_metal(const orc_scene& s, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {
+    prd.emitted = v3(0.f);
+    prd.is_specular = true;
+    prd.materialType = RTW_MAT_METAL;
+    prd.hit_normal = h.normal;
+    V3 reflected = reflect(direction, h.normal);
+    V3 scatterDirection = reflected + m.param * randomInUnitSphere(prd.seed);
+    prd.scattered_origin = h.point;
+    prd.scattered_direction = normalize(scatterDirection);
+    prd.scattered_pdf = 0.f;
+    prd.attenuation = texture_eval(s, m.texture, h.u, h.v, h.point);
+    if (dot(prd.scattered_direction, h.normal) <= 0.0f) {
+        prd.scatterEvent = Ray_Cancel;
+        return;
+    }
+    prd.pdf = 1.f;
+    prd.scatterEvent = Ray_Hit;
+}
+// material/dielectricMaterial.cu:20-26
+static inline float fresnelSchlick(float cosThetaI, float etaI, float etaT) {
+    float r0 = (etaI - etaT) / (etaI + etaT);
+    r0 = r0 * r0;
+    return r0 + (1.f - r0) * powf((1.f - cosThetaI), 5.f);
+}
+// material/dielectricMaterial.cu:37-114
+static void mat_dielectric(const orc_scene&, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {
+    V3 unitDirection = normalize(-prd.lightDirection);
+    V3 localNormal;
+    float etaI, etaT;
+    if (dot(direction, h.normal) < 0.0f) {
+        localNormal = h.normal;
+        etaI = 1.0f;
+        etaT = m.param;
+    } else {
+        localNormal = -h.normal;
+        etaI = m.param;
+        etaT = 1.0f;
+    }
+    V3 scatterDirection;
+    float cosThetaI = fminf(dot(-unitDirection, localNormal), 1.0f);
+    float sinThetaI = sqrtf(1.0f - cosThetaI * cosThetaI);
+    if (((etaI / etaT) * sinThetaI) > 1.0f) {
+        scatterDirection = reflect(unitDirection, localNormal);
+    } else {
+        float reflectProb = fresnelSchlick(cosThetaI, etaI, etaT);
+        if (rnd(prd.seed) < reflectProb) {
+            scatterDirection = reflect(unitDirection, localNormal);
+        } else {
+            float sinThetaT = fminf((etaI / etaT) * sinThetaI, 1.0f);
+            float cosThetaT = sqrtf(1.0f - sinThetaT * sinThetaT);
+            scatterDirection = (etaI / etaT) * (unitDirection + cosThetaI * localNormal) - cosThetaT * localNormal;
+        }
+    }
+    prd.emitted = v3(0.f);
+    prd.is_specular = true;
+    prd.materialType = RTW_MAT_DIELECTRIC;
+    prd.scatterEvent = Ray_Hit;
+    prd.scattered_origin = h.point;
+    prd.scattered_direction = scatterDirection;
+    prd.attenuation = v3(1.0f, 1.0f, 1.0f);
+    prd.scattered_pdf = 0.f;
+    prd.hit_normal = h.normal;
+    prd.pdf = 1.f;
+}
+// material/diffuseLight.cu:48-69
+static void mat_diffuse_light(const orc_scene& s, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {
+    if (dot(h.normal, direction) < 0.f) prd.emitted = texture_eval(s, m.texture, h.u, h.v, h.point);
+    else prd.emitted = v3(0.f);
+    prd.is_specular = false;
+    prd.materialType = RTW_MAT_DIFFUSE_LIGHT;
+    prd.hit_normal = h.normal;
+    prd.scatterEvent = Ray_Cancel;
+    prd.scattered_pdf = 0.f;
+    prd.radiance = prd.emitted;
+}
+// material/isotropicMaterial.cu:30-51
+static void mat_isotropic(const orc_scene& s, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {
+    (void)direction;
+    V3 scatterDirection = randomInUnitSphere(prd.seed);
+    prd.is_specular = true;
+    prd.materialType = RTW_MAT_ISOTROPIC;
+    prd.scatterEvent = Ray_Hit;
+    prd.hit_normal = h.normal;
+    prd.scattered_origin = h.point;
+    prd.scattered_direction = scatterDirection;
+    prd.emitted = v3(0.f);
+    prd.attenuation = texture_eval(s, m.texture, h.u, h.v, h.point);
+    prd.scattered_pdf = 0.f;
+}
+// material/normalMaterial.cu:21-31
+static void mat_normal(const orc_scene&, const rtw_material&, PerRayData& prd, V3, const HitRecord& h) {
+    prd.emitted = v3(0.f);
+    prd.is_specular = true;
+    prd.materialType = RTW_MAT_NORMAL;
+    prd.hit_normal = h.normal;
+    prd.scatterEvent = Ray_Finish;
+    prd.attenuation = 0.5f * (h.normal + v3(1.0f, 1.0f, 1.0f));
+}
+
+// ============================================================================
+// Light sampling (pdf/rectPdf.cu:124-193 via pdf/mixturePdf.cu:25-38; Q26)
+// ============================================================================
+struct LightSample {  // raydata.cuh:51-58
+    V3 position;
+    float distance;
+    V3 direction;
+    V3 emission;
+    float pdf;
+};
+static LightSample rect_generate(const orc_scene& s, const rtw_light& light, V3 origin, uint32_t& seed) {
+    const rtw_light_rect& rc = s.light_rect;
+    // draws sequenced a-axis then b-axis (SURVEY §7b caveat)
+    float ra = rnd(seed);
+    float rb = rnd(seed);
+    float pa = rc.a0 + ra * (rc.a1 - rc.a0);
+    float pb = rc.b0 + rb * (rc.b1 - rc.b0);
+    V3 random_point;
+    if (rc.axis == 0) random_point = v3(rc.k, pa, pb);        // rect_x_generate: rectPdf.cu:124-145
+    else if (rc.axis == 1) random_point = v3(pa, rc.k, pb);   // rect_y_generate: rectPdf.cu:147-169
+    else random_point = v3(pa, pb, rc.k);                     // rect_z_generate: rectPdf.cu:171-193
+    LightSample ls;
+    ls.direction = random_point - origin;
+    ls.position = random_point;
+    ls.distance = length(ls.direction);
+    ls.pdf = 0.f;
+    ls.emission = v3(0.f);
+    if (ls.distance > 1.0e-6f) {
+        ls.direction /= ls.distance;
+        const float costa = dot(-ls.direction, v3(light.normal));
+        if (costa > 1.0e-6f) {
+            ls.emission = v3(light.emission) * (float)(int)s.lights.size();
+            ls.pdf = ls.distance * ls.distance / (light.area * costa);
+        }
+    }
+    return ls;
+}
+
+// lib/raydata.cuh:166-170
+static inline float powerHeuristic(float a, float b) {
+    const float t = a * a;
+    return t / (t + b * b);
+}
+static inline bool isNotNull(V3 v) { return (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f); }
+
+// ============================================================================
+// __closesthit__radiance (shaders/closehit.cu:45-121) and __miss__Program
+// (miss/miss.cu:8-30)
+// ============================================================================
+static void closest_hit(const orc_scene& s, int prim, const Ray& ray, float t, PerRayData& prd, int mode, Counters& c) {
+    c.vertices++;
+    HitRecord hit;
+    hit_attributes(s, prim, ray, t, hit);
+    V3 direction = ray.d;
+    prd.distance = t;
+    const rtw_material& m = s.mats[s.prims[prim].material];
+    prd.radiance = v3(0.f);
+    switch (m.type) {
+    case RTW_MAT_LAMBERTIAN: mat_lambertian(s, m, prd, direction, hit); break;
+    case RTW_MAT_DIFFUSE_LIGHT: mat_diffuse_light(s, m, prd, direction, hit); break;
+    case RTW_MAT_METAL: mat_metal(s, m, prd, direction, hit); break;
+    case RTW_MAT_DIELECTRIC: mat_dielectric(s, m, prd, direction, hit); break;
+    case RTW_MAT_ISOTROPIC: mat_isotropic(s, m, prd, direction, hit); break;
+    default: mat_normal(s, m, prd, direction, hit); break;
+    }
+    const int numLights = (int)s.lights.size();
+    if (prd.scatterEvent != Ray_Miss && prd.scatterEvent != Ray_Finish && prd.scatterEvent != Ray_Cancel &&
+        !prd.is_specular && numLights > 0 && s.has_light_rect) {
+        int indexLight = 0;
+        if (1 < numLights) {
+            int v = (int)floorf(rnd(prd.seed) * numLights);
+            indexLight = std::min(std::max(v, 0), numLights - 1);
+        }
+        LightSample ls = rect_generate(s, s.lights[indexLight], prd.scattered_origin, prd.seed);
+        if (ls.pdf > 0) {
+            // eval_bsdf_diffuse_reflection, material/lambertianMaterial.cu:74-81 (Q15: only reachable one)
+            V3 f = prd.attenuation * kInvPi;
+            float bpdf = fmaxf(0.0f, dot(ls.direction, prd.hit_normal) * kInvPi);
+            if (0.0f < bpdf && isNotNull(f)) {
+                Ray sh;
+                sh.o = prd.scattered_origin;
+                sh.d = ls.direction;
+                sh.tmin = 500 * 1.0e-7f;
+                sh.tmax = ls.distance - 500 * 1.0e-7f;
+                sh.time = 0.0f;
+                sh.gather_time = prd.gatherTime;
+                sh.seed = prd.seed;
+                bool occluded = trace_any(s, sh, mode, c);
+                if (!occluded) {
+                    const float weight = powerHeuristic(ls.pdf, bpdf);
+                    prd.radiance += f * ls.emission * (weight * dot(ls.direction, prd.hit_normal) / ls.pdf);
+                }
+            }
+        }
+    }
+}
+
+static void miss_program(const orc_scene& s, PerRayData& prd) {
+    prd.emitted = v3(0.f);
+    if (s.sky_light) {
+        V3 unitDirection = normalize(prd.scattered_direction);
+        float t = 0.5f * (unitDirection.y + 1.0f);
+        prd.radiance = (1.0f - t) * v3(1.0f, 1.0f, 1.0f) + t * v3(0.5f, 0.7f, 1.0f);
+    } else {
+        prd.radiance = v3(0.0f);
+    }
+    prd.scatterEvent = Ray_Miss;
+}
+
+// ============================================================================
+// __raygen__Program (raygen/raygen.cu:123-159) for sample k of pixel (x, y)
+// ============================================================================
+static void camera_ray(const orc_scene& s, int Nx, int Ny, int x, int y, int k, uint32_t& seed, V3& origin, V3& direction) {
+    seed = tea_n(64, (uint32_t)Nx * (uint32_t)y + (uint32_t)x, (uint32_t)k);  // raygen.cu:129 (Q1: k = 0 in the reference)
+    float sx = float((float)(uint32_t)x + rnd(seed)) / float((uint32_t)Nx);  // raygen.cu:134
+    float ty = float((float)(uint32_t)y + rnd(seed)) / float((uint32_t)Ny);  // raygen.cu:135
+    // shaders/camera.cu:11-19 (Q3: lens radius 0 still burns two draws)
+    const rtw_camera& cm = s.cam;
+    V3 rd = cm.lens_radius * random_in_unit_disk(seed);
+    V3 lens_offset = v3(cm.u) * rd.x + v3(cm.v) * rd.y;
+    origin = v3(cm.origin) + lens_offset;
+    direction = v3(cm.lower_left) + (sx * v3(cm.horizontal)) + (ty * v3(cm.vertical)) - origin;
+}
+
+static V3 sample_radiance(const orc_scene& s, int Nx, int Ny, int x, int y, int k, int max_depth, int mode, Counters& c) {
+    uint32_t seed;
+    V3 origin, direction;
+    camera_ray(s, Nx, Ny, x, y, k, seed, origin, direction);
+    PerRayData prd{};
+    prd.scattered_origin = origin;
+    prd.scattered_direction = direction;
+    // color(): raygen.cu:89-105 (Q4)
+    prd.seed = seed;
+    prd.gatherTime = s.cam.time0 + rnd(seed) * (s.cam.time1 - s.cam.time0);
+    // rayColor(): raygen.cu:28-87
+    uint32_t lseed = prd.seed;
+    V3 throughput = v3(1.0f);
+    V3 sampleRadiance = v3(0.f);
+    int depth = 0;
+    while (depth < max_depth) {
+        prd.lightDirection = -direction;
+        Ray ray;
+        ray.o = origin;
+        ray.d = direction;
+        ray.tmin = 1e-6f;
+        ray.tmax = 1.e27f;  // shaders/appconfig.h:3
+        ray.time = rnd(lseed);
+        ray.gather_time = prd.gatherTime;
+        ray.seed = prd.seed;
+        float t; int prim;
+        if (trace_closest(s, ray, mode, t, prim, c)) closest_hit(s, prim, ray, t, prd, mode, c);
+        else miss_program(s, prd);
+        sampleRadiance += prd.radiance * throughput;
+        if (prd.scatterEvent == Ray_Miss || prd.scatterEvent == Ray_Finish || prd.scatterEvent == Ray_Cancel) break;
+        origin = prd.scattered_origin;
+        direction = prd.scattered_direction;
+        throughput *= prd.attenuation;
+        if (2 <= depth) {
+            const float probability = fmaxf3(throughput);
+            if (probability < rnd(prd.seed)) break;
+            throughput /= probability;
+        }
+        depth++;
+    }
+    c.paths++;
+    // removeNaNs: raygen.cu:17-24
+    if (!(sampleRadiance.x == sampleRadiance.x)) sampleRadiance.x = 0.0f;
+    if (!(sampleRadiance.y == sampleRadiance.y)) sampleRadiance.y = 0.0f;
+    if (!(sampleRadiance.z == sampleRadiance.z)) sampleRadiance.z = 0.0f;
+    return sampleRadiance;
+}
+
+extern "C" void orc_sample_radiance(const orc_scene* s, int Nx, int Ny, int x, int y, int k, int max_depth,
+                                    int mode, float* rgb) {
+    Counters c;
+    V3 r = sample_radiance(*s, Nx, Ny, x, y, k, max_depth, mode, c);
+    rgb[0] = r.x; rgb[1] = r.y; rgb[2] = r.z;
+}
+
+extern "C" void orc_camera_rays(const orc_scene* s, int Nx, int Ny, int sample, rtw_ray* out) {
+    for (int y = 0; y < Ny; y++)
+        for (int x = 0; x < Nx; x++) {
+            uint32_t seed;
+            V3 o, d;
+            camera_ray(*s, Nx, Ny, x, y, sample, seed, o, d);
+            uint32_t s4 = seed;
+            float gather = s->cam.time0 + rnd(seed) * (s->cam.time1 - s->cam.time0);
+            uint32_t l = s4;
+            rtw_ray& r = out[(size_t)y * Nx + x];
+            r.origin[0] = o.x; r.origin[1] = o.y; r.origin[2] = o.z;
+            r.dir[0] = d.x; r.dir[1] = d.y; r.dir[2] = d.z;
+            r.tmin = 1e-6f; r.tmax = 1.e27f;
+            r.time = rnd(l);
+            r.gather_time = gather;
+            r.seed = s4;
+            r.pad = 0;
+        }
+}
+
+extern "C" int orc_render_rows(const orc_scene* s, int Nx, int Ny, int y0, int y1, int sample_first,
+                               int sample_stride, int sample_count, int max_depth, int n_threads, int mode,
+                               float* rgba_sum, orc_counters* counters) {
+    if (!s || Nx <= 0 || Ny <= 0 || !rgba_sum) return 1;
+    if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
+    if (n_threads <= 0) n_threads = 1;
+    std::atomic<int> next_row(y0);
+    std::vector<Counters> cs(n_threads);
+    auto worker = [&](int tid) {
+        Counters& c = cs[tid];
+        for (;;) {
+            int y = next_row.fetch_add(1);
+            if (y >= y1) break;
+            for (int x = 0; x < Nx; x++) {
+                V3 acc = v3(0.f);
+                for (int i = 0; i < sample_count; i++) {
+                    int k = sample_first + i * sample_stride;
+                    acc += sample_radiance(*s, Nx, Ny, x, y, k, max_depth, mode, c);
+                }
+                float* o = rgba_sum + ((size_t)y * Nx + x) * 4;
+                o[0] += acc.x; o[1] += acc.y; o[2] += acc.z; o[3] += (float)sample_count;
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int i = 0; i < n_threads; i++) th.emplace_back(worker, i);
+    for (auto& t : th) t.join();
+    for (auto& c : cs) c.add_to(counters);
+    return 0;
+}
+
+extern "C" int orc_render(const orc_scene* s, int Nx, int Ny, int sample_first, int sample_stride, int sample_count,
+                          int max_depth, int n_threads, int mode, float* rgba_sum, orc_counters* counters) {
+    return orc_render_rows(s, Nx, Ny, 0, Ny, sample_first, sample_stride, sample_count, max_depth, n_threads, mode,
+                           rgba_sum, counters);
+}
+
+extern "C" void orc_tonemap(int n_pixels, int spp, const float* sum, float* out) {
+    for (int i = 0; i < n_pixels; i++) {
+        // raygen.cu:144-158; with spp samples the mean replaces the single sample (Q1)
+        float inv = 1.0f / (float)spp;
+        out[i * 4 + 0] = sqrtf(sum[i * 4 + 0] * inv);
+        out[i * 4 + 1] = sqrtf(sum[i * 4 + 1] * inv);
+        out[i * 4 + 2] = sqrtf(sum[i * 4 + 2] * inv);
+        out[i * 4 + 3] = 1.f;
+    }
+}

@@ -1,0 +1,88 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement of the reference's path-tracing launch
+ * (reference RestOfLife/Director.cpp:982 → raygen/raygen.cu:123 and everything
+ * below it).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this library.  The product
+ * (raytracing-weekend_b200/) never includes, links or calls anything in oracle/.
+ *
+ * PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for
+ * this path and none of its device code compiles here (every file needs optix.h,
+ * SURVEY.md §8c).  The only source-pinned pieces are tea<N>/xorshift32/randf
+ * (lib/random.cuh compiles standalone; KATs in tests/golden/rng_kat.json were
+ * produced by compiling THAT file, see oracle/ref_rng_kat.sh).  Everything else
+ * is a statement-by-statement restatement, each function citing file:line.
+ *
+ * The scene description consumed here is the C-ABI POD of include/rtw.h.
+ */
+#ifndef ORACLE_H
+#define ORACLE_H
+#include <stdint.h>
+#include "../include/rtw.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orc_scene orc_scene;
+
+typedef struct orc_counters {
+    uint64_t paths;
+    uint64_t rays_closest;
+    uint64_t rays_shadow;
+    uint64_t nodes_visited;      /* BVH mode only */
+    uint64_t prims_tested;
+    uint64_t vertices_shaded;    /* closest-hit shader invocations */
+    uint64_t shadow_enqueued;    /* == rays_shadow */
+} orc_counters;
+
+/* ---- RNG (lib/random.cuh:7-38; SDK cuda/random.h lcg/rnd) ---- */
+uint32_t orc_tea(uint32_t rounds, uint32_t s0, uint32_t s1);
+void orc_rng_stream(uint32_t seed0, uint32_t seed1, int n,
+                    uint32_t* tea_out, uint32_t* lcg_out, float* rnd_out,
+                    uint32_t* xs_out, float* randf_out);
+
+/* ---- scene ---- */
+int  orc_scene_load(const rtw_scene_desc* desc, orc_scene** out);   /* deep copy */
+void orc_scene_free(orc_scene* s);
+
+/* ---- rays ---- */
+void orc_camera_rays(const orc_scene* s, int Nx, int Ny, int sample, rtw_ray* out);
+/* mode 0 = brute force over all primitives (ground truth), 1 = host-mirror LBVH */
+void orc_trace_closest(const orc_scene* s, const rtw_ray* rays, int n, rtw_hit* hits,
+                       int mode, orc_counters* counters);
+void orc_trace_any(const orc_scene* s, const rtw_ray* rays, int n, int32_t* occluded,
+                   int mode, orc_counters* counters);
+
+/* ---- render: linear sums (r,g,b,count) per pixel, row 0 = bottom ---- */
+int  orc_render(const orc_scene* s, int Nx, int Ny,
+                int sample_first, int sample_stride, int sample_count,
+                int max_depth, int n_threads, int mode,
+                float* rgba_sum, orc_counters* counters);
+/* rows [y0,y1) only (bounded CPU-baseline samples) */
+int  orc_render_rows(const orc_scene* s, int Nx, int Ny, int y0, int y1,
+                     int sample_first, int sample_stride, int sample_count,
+                     int max_depth, int n_threads, int mode,
+                     float* rgba_sum, orc_counters* counters);
+/* out = (sqrt(sum/spp), 1)  (raygen/raygen.cu:144-158) */
+void orc_tonemap(int n_pixels, int spp, const float* rgba_sum, float* rgba_out);
+/* single sample radiance, for debugging and per-path tests */
+void orc_sample_radiance(const orc_scene* s, int Nx, int Ny, int x, int y, int k,
+                         int max_depth, int mode, float* rgb_out);
+
+/* ---- host-mirror LBVH (same algorithm as the device builder) ---- */
+int  orc_bvh_build(orc_scene* s);
+int  orc_bvh_info(const orc_scene* s, rtw_bvh_info* info);
+int  orc_bvh_download(const orc_scene* s, uint64_t* morton, int32_t* leaf_prim,
+                      int32_t* left, int32_t* right, float* bounds);
+/* per-primitive world AABBs as the builder sees them: 6 floats per prim */
+void orc_prim_aabbs(const orc_scene* s, float* aabbs);
+
+/* texture evaluation hook (tests) */
+void orc_texture_eval(const orc_scene* s, int texture, float u, float v,
+                      const float* p, float* rgb_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
