@@ -543,7 +543,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
         BvhNode& nd = s->nodes[0];
         nd.left = ~0; nd.right = ~0; nd.parent = -1;
         nd.lmin = boxes[s->leaf_prim[0]].mn; nd.lmax = boxes[s->leaf_prim[0]].mx;
-        nd.rmin = v3(FLT_MAX); nd.rmax = v3(-FLT_MAX);  // empty: never entered
+        nd.rmin = v3(FLT_MAX); nd.rmax = v3(FLT_MAX);  // unreachable point box
         s->bvh_built = true;
         return 0;
     }

@@ -1,0 +1,369 @@
+// rtw_api.cu — C-ABI: context lifetime, scene upload, LBVH build.
+// (render entry points: rtw_render.cu; test hooks: rtw_hooks.cu)
+//
+// Replaces Director::init / createScene / destroy of the reference
+// (Director.cpp:33-104, 951-969; Director.h:120-126): no OptiX context, modules,
+// program groups, pipeline or SBT — the "ABI" towards the device is the DScene
+// struct passed by value to every kernel.
+#include "rtw_ctx.h"
+
+#include <cstring>
+
+using namespace rtw;
+
+static std::string g_create_error;
+
+extern "C" int rtw_abi_version(void) { return RTW_ABI_VERSION; }
+
+extern "C" int rtw_device_count(int* count) {
+    if (!count) return RTW_ERR_INVALID;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *count = 0;
+        g_create_error = std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        return RTW_ERR_NO_DEVICE;
+    }
+    *count = n;
+    return RTW_OK;
+}
+
+extern "C" const char* rtw_last_error(const rtw_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int rtw_create(int device, rtw_ctx** out) {
+    if (!out) return RTW_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    int rc = rtw_device_count(&n);
+    if (rc != RTW_OK || n <= 0) {
+        if (rc == RTW_OK) g_create_error = "no CUDA device visible (this library has no CPU fallback)";
+        return RTW_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) {
+        g_create_error = "device index out of range";
+        return RTW_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
+        return RTW_ERR_CUDA;
+    }
+    rtw_ctx* c = new rtw_ctx();
+    c->device = device;
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_begin);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_end);
+    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ring_events[i], cudaEventDisableTiming);
+    for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreate(&c->stage_events[i]);
+    if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&c->h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8);
+    if (e != cudaSuccess) {
+        g_create_error = std::string("context setup: ") + cudaGetErrorString(e);
+        delete c;
+        return RTW_ERR_CUDA;
+    }
+    *out = c;
+    return RTW_OK;
+}
+
+static void free_frame(rtw_ctx* c) {
+    if (c->d_accum) cudaFree(c->d_accum);
+    if (c->d_out) cudaFree(c->d_out);
+    c->d_accum = nullptr;
+    c->d_out = nullptr;
+    c->frame_pixels = 0;
+}
+
+extern "C" int rtw_destroy(rtw_ctx* c) {
+    if (!c) return RTW_ERR_INVALID;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    dfree_all(c->scene_allocs);
+    dfree_all(c->wave_allocs);
+    free_frame(c);
+    if (c->h_counters) cudaFreeHost(c->h_counters);
+    for (auto& e : c->ring_events) if (e) cudaEventDestroy(e);
+    for (auto& e : c->stage_events) if (e) cudaEventDestroy(e);
+    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return RTW_OK;
+}
+
+extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
+    if (!c || !name) return RTW_ERR_INVALID;
+    if (!strcmp(name, "pool_paths")) {
+        if (value < 1024 || value > (1ll << 26)) return fail(c, RTW_ERR_INVALID, "pool_paths out of range [1024, 2^26]");
+        c->opt_pool_paths = value;
+    } else if (!strcmp(name, "top_nodes")) {
+        if (value < 0 || value > 3584) return fail(c, RTW_ERR_INVALID, "top_nodes out of range [0, 3584]");
+        c->opt_top_nodes = (int)value;
+    } else if (!strcmp(name, "profile")) {
+        c->opt_profile = value ? 1 : 0;
+    } else if (!strcmp(name, "lag")) {
+        if (value < 1 || value > 7) return fail(c, RTW_ERR_INVALID, "lag out of range [1, 7]");
+        c->opt_lag = (int)value;
+    } else {
+        return fail(c, RTW_ERR_INVALID, std::string("unknown option ") + name);
+    }
+    return RTW_OK;
+}
+
+extern "C" int rtw_get_stats(rtw_ctx* c, rtw_stats* out) {
+    if (!c || !out) return RTW_ERR_INVALID;
+    *out = c->stats;
+    return RTW_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Scene upload: flat tables of Director::initLaunchParams / createSBT
+// (Director.cpp:483-553, 659-848) without the per-record cudaMalloc churn.
+// ---------------------------------------------------------------------------
+static int validate_scene(rtw_ctx* c, const rtw_scene_desc* d) {
+    if (d->n_prims <= 0 || !d->prims) return fail(c, RTW_ERR_INVALID, "scene has no primitives");
+    if (d->n_prims > (int)RTW_REF_MASK) return fail(c, RTW_ERR_INVALID, "too many primitives");
+    if (d->n_materials <= 0 || !d->materials) return fail(c, RTW_ERR_INVALID, "scene has no materials");
+    if (d->n_lights > RTW_MAX_LIGHTS) return fail(c, RTW_ERR_INVALID, "more than RTW_MAX_LIGHTS lights");
+    for (int i = 0; i < d->n_prims; i++) {
+        const rtw_prim& p = d->prims[i];
+        if (p.type < 0 || p.type >= RTW_PRIM_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad primitive type");
+        if (p.material < 0 || p.material >= d->n_materials) return fail(c, RTW_ERR_INVALID, "primitive material out of range");
+        if (p.transform >= d->n_transforms) return fail(c, RTW_ERR_INVALID, "primitive transform out of range");
+    }
+    for (int i = 0; i < d->n_materials; i++) {
+        const rtw_material& m = d->materials[i];
+        if (m.type < 0 || m.type >= RTW_MAT_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad material type");
+        if (m.texture >= d->n_textures) return fail(c, RTW_ERR_INVALID, "material texture out of range");
+    }
+    for (int i = 0; i < d->n_textures; i++) {
+        const rtw_texture& t = d->textures[i];
+        if (t.type < 0 || t.type >= RTW_TEX_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad texture type");
+        if (t.type == RTW_TEX_NOISE && (t.perlin < 0 || t.perlin >= d->n_perlin)) return fail(c, RTW_ERR_INVALID, "noise table out of range");
+        if (t.type == RTW_TEX_IMAGE && (t.image < 0 || t.image >= d->n_images)) return fail(c, RTW_ERR_INVALID, "image out of range");
+        if (t.type == RTW_TEX_CHECKER && (t.odd >= d->n_textures || t.even >= d->n_textures)) return fail(c, RTW_ERR_INVALID, "checker child out of range");
+    }
+    return RTW_OK;
+}
+
+extern "C" int rtw_upload_scene(rtw_ctx* c, const rtw_scene_desc* d) {
+    if (!c || !d) return RTW_ERR_INVALID;
+    int rc = validate_scene(c, d);
+    if (rc != RTW_OK) return rc;
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    dfree_all(c->scene_allocs);
+    c->scene_loaded = false;
+    c->accel_built = false;
+    c->scene = DScene{};
+    c->build = BuildBuffers{};
+    auto& pool = c->scene_allocs;
+    const int n = d->n_prims;
+    c->n_prims = n;
+    c->n_xforms = d->n_transforms;
+    c->n_mats = d->n_materials;
+
+    // raw arrays for the builder
+    rtw_prim* d_prims = nullptr;
+    rtw_transform* d_xf = nullptr;
+    rtw_material* d_mats_raw = nullptr;
+    RTW_CUDA(c, dalloc(pool, &d_prims, n));
+    RTW_CUDA(c, cudaMemcpyAsync(d_prims, d->prims, sizeof(rtw_prim) * n, cudaMemcpyHostToDevice, c->stream));
+    if (d->n_transforms > 0) {
+        RTW_CUDA(c, dalloc(pool, &d_xf, d->n_transforms));
+        RTW_CUDA(c, cudaMemcpyAsync(d_xf, d->transforms, sizeof(rtw_transform) * d->n_transforms, cudaMemcpyHostToDevice, c->stream));
+    }
+    RTW_CUDA(c, dalloc(pool, &d_mats_raw, d->n_materials));
+    RTW_CUDA(c, cudaMemcpyAsync(d_mats_raw, d->materials, sizeof(rtw_material) * d->n_materials, cudaMemcpyHostToDevice, c->stream));
+    c->build.prims = d_prims;
+    c->build.xforms = d_xf;
+    c->build.mats_raw = d_mats_raw;
+    c->build.n = n;
+
+    // shading tables in their float4 device layout
+    DScene& sc = c->scene;
+    std::vector<float4> xf4((size_t)6 * (d->n_transforms > 0 ? d->n_transforms : 1));
+    for (int i = 0; i < d->n_transforms; i++) {
+        const rtw_transform& t = d->transforms[i];
+        for (int r = 0; r < 3; r++) {
+            xf4[6 * i + r] = make_float4(t.w2o[4 * r], t.w2o[4 * r + 1], t.w2o[4 * r + 2], t.w2o[4 * r + 3]);
+            xf4[6 * i + 3 + r] = make_float4(t.o2w[4 * r], t.o2w[4 * r + 1], t.o2w[4 * r + 2], t.o2w[4 * r + 3]);
+        }
+    }
+    float4* d_xf4 = nullptr;
+    RTW_CUDA(c, dalloc(pool, &d_xf4, xf4.size()));
+    RTW_CUDA(c, cudaMemcpyAsync(d_xf4, xf4.data(), sizeof(float4) * xf4.size(), cudaMemcpyHostToDevice, c->stream));
+    sc.xforms = d_xf4;
+
+    std::vector<float4> mats(d->n_materials);
+    for (int i = 0; i < d->n_materials; i++)
+        mats[i] = make_float4(u2f((uint32_t)d->materials[i].type), u2f((uint32_t)d->materials[i].texture), d->materials[i].param, 0.f);
+    float4* d_mats = nullptr;
+    RTW_CUDA(c, dalloc(pool, &d_mats, mats.size()));
+    RTW_CUDA(c, cudaMemcpyAsync(d_mats, mats.data(), sizeof(float4) * mats.size(), cudaMemcpyHostToDevice, c->stream));
+    sc.mats = d_mats;
+
+    std::vector<float4> texs((size_t)2 * (d->n_textures > 0 ? d->n_textures : 1));
+    for (int i = 0; i < d->n_textures; i++) {
+        const rtw_texture& t = d->textures[i];
+        texs[2 * i] = make_float4(u2f((uint32_t)t.type), t.color[0], t.color[1], t.color[2]);
+        const int idx = t.type == RTW_TEX_NOISE ? t.perlin : t.image;
+        texs[2 * i + 1] = make_float4(u2f((uint32_t)t.odd), u2f((uint32_t)t.even), t.scale, u2f((uint32_t)idx));
+    }
+    float4* d_texs = nullptr;
+    RTW_CUDA(c, dalloc(pool, &d_texs, texs.size()));
+    RTW_CUDA(c, cudaMemcpyAsync(d_texs, texs.data(), sizeof(float4) * texs.size(), cudaMemcpyHostToDevice, c->stream));
+    sc.texs = d_texs;
+
+    if (d->n_perlin > 0) {
+        std::vector<float4> vec((size_t)256 * d->n_perlin);
+        std::vector<int> perm((size_t)768 * d->n_perlin);
+        for (int t = 0; t < d->n_perlin; t++) {
+            const rtw_perlin& p = d->perlin[t];
+            for (int i = 0; i < 256; i++) {
+                vec[256 * t + i] = make_float4(p.ranvec[i][0], p.ranvec[i][1], p.ranvec[i][2], 0.f);
+                perm[768 * t + i] = p.perm_x[i];
+                perm[768 * t + 256 + i] = p.perm_y[i];
+                perm[768 * t + 512 + i] = p.perm_z[i];
+            }
+        }
+        float4* d_vec = nullptr;
+        int* d_perm = nullptr;
+        RTW_CUDA(c, dalloc(pool, &d_vec, vec.size()));
+        RTW_CUDA(c, dalloc(pool, &d_perm, perm.size()));
+        RTW_CUDA(c, cudaMemcpyAsync(d_vec, vec.data(), sizeof(float4) * vec.size(), cudaMemcpyHostToDevice, c->stream));
+        RTW_CUDA(c, cudaMemcpyAsync(d_perm, perm.data(), sizeof(int) * perm.size(), cudaMemcpyHostToDevice, c->stream));
+        RTW_CUDA(c, cudaStreamSynchronize(c->stream));  // host vectors go out of scope
+        sc.perlin_vec = d_vec;
+        sc.perlin_perm = d_perm;
+    }
+    if (d->n_images > 0) {
+        std::vector<DImage> imgs(d->n_images);
+        for (int i = 0; i < d->n_images; i++) {
+            const rtw_image& im = d->images[i];
+            if (im.width <= 0 || im.height <= 0 || !im.rgba) return fail(c, RTW_ERR_INVALID, "bad image");
+            uchar4* d_tex = nullptr;
+            RTW_CUDA(c, dalloc(pool, &d_tex, (size_t)im.width * im.height));
+            RTW_CUDA(c, cudaMemcpyAsync(d_tex, im.rgba, (size_t)im.width * im.height * 4, cudaMemcpyHostToDevice, c->stream));
+            imgs[i].texels = d_tex;
+            imgs[i].width = im.width;
+            imgs[i].height = im.height;
+        }
+        DImage* d_imgs = nullptr;
+        RTW_CUDA(c, dalloc(pool, &d_imgs, imgs.size()));
+        RTW_CUDA(c, cudaMemcpyAsync(d_imgs, imgs.data(), sizeof(DImage) * imgs.size(), cudaMemcpyHostToDevice, c->stream));
+        RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+        sc.images = d_imgs;
+        sc.has_images = 1;
+    }
+
+    // flags, lights, camera
+    c->class_mask = 1u << RTW_Q_TERMINAL;
+    for (int i = 0; i < n; i++) {
+        const int pt = d->prims[i].type;
+        if (pt == RTW_PRIM_VOLUME_BOX || pt == RTW_PRIM_VOLUME_SPHERE) sc.has_media = 1;
+        if (pt == RTW_PRIM_MOVING_SPHERE) sc.has_motion = 1;
+        switch (d->materials[d->prims[i].material].type) {
+        case RTW_MAT_LAMBERTIAN: c->class_mask |= 1u << RTW_Q_LAMBERTIAN; break;
+        case RTW_MAT_METAL: c->class_mask |= 1u << RTW_Q_METAL; break;
+        case RTW_MAT_DIELECTRIC: c->class_mask |= 1u << RTW_Q_DIELECTRIC; break;
+        case RTW_MAT_ISOTROPIC: c->class_mask |= 1u << RTW_Q_ISOTROPIC; break;
+        default: break;
+        }
+    }
+    sc.n_lights = d->n_lights;
+    sc.sky_light = d->sky_light;
+    sc.has_light_rect = d->has_light_rect;
+    sc.rect_axis = d->light_rect.axis;
+    sc.rect_a0 = d->light_rect.a0; sc.rect_a1 = d->light_rect.a1;
+    sc.rect_b0 = d->light_rect.b0; sc.rect_b1 = d->light_rect.b1;
+    sc.rect_k = d->light_rect.k;
+    for (int i = 0; i < d->n_lights; i++) {
+        const rtw_light& l = d->lights[i];
+        sc.lights[i].normal = f3(l.normal[0], l.normal[1], l.normal[2]);
+        sc.lights[i].area = l.area;
+        sc.lights[i].emission = f3(l.emission[0], l.emission[1], l.emission[2]);
+        sc.lights[i].pad = 0.f;
+    }
+    const rtw_camera& cm = d->camera;
+    sc.cam_origin = f3(cm.origin[0], cm.origin[1], cm.origin[2]);
+    sc.cam_u = f3(cm.u[0], cm.u[1], cm.u[2]);
+    sc.cam_v = f3(cm.v[0], cm.v[1], cm.v[2]);
+    sc.cam_ll = f3(cm.lower_left[0], cm.lower_left[1], cm.lower_left[2]);
+    sc.cam_horizontal = f3(cm.horizontal[0], cm.horizontal[1], cm.horizontal[2]);
+    sc.cam_vertical = f3(cm.vertical[0], cm.vertical[1], cm.vertical[2]);
+    sc.cam_lens_radius = cm.lens_radius;
+    sc.cam_time0 = cm.time0;
+    sc.cam_time1 = cm.time1;
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));  // borrowed host arrays are free again
+    c->scene_loaded = true;
+    return RTW_OK;
+}
+
+// ---------------------------------------------------------------------------
+// LBVH build (replaces all optixAccelBuild call sites)
+// ---------------------------------------------------------------------------
+extern "C" int rtw_build_accel(rtw_ctx* c) {
+    if (!c) return RTW_ERR_INVALID;
+    if (!c->scene_loaded) return fail(c, RTW_ERR_STATE, "rtw_build_accel before rtw_upload_scene");
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    auto& pool = c->scene_allocs;
+    BuildBuffers& b = c->build;
+    const int n = b.n;
+    const int ni = n > 1 ? n - 1 : 1;
+    if (!b.box_mn) {  // first build for this scene: allocate
+        RTW_CUDA(c, dalloc(pool, &b.box_mn, n));
+        RTW_CUDA(c, dalloc(pool, &b.box_mx, n));
+        RTW_CUDA(c, dalloc(pool, &b.bounds, 8));
+        RTW_CUDA(c, dalloc(pool, &b.keys[0], n));
+        RTW_CUDA(c, dalloc(pool, &b.keys[1], n));
+        RTW_CUDA(c, dalloc(pool, &b.vals[0], n));
+        RTW_CUDA(c, dalloc(pool, &b.vals[1], n));
+        RTW_CUDA(c, dalloc(pool, &b.hist, (size_t)256 * sort_num_blocks(n) + 1024));
+        RTW_CUDA(c, dalloc(pool, &b.parent, ni));
+        RTW_CUDA(c, dalloc(pool, &b.leaf_parent, n));
+        RTW_CUDA(c, dalloc(pool, &b.flags, ni));
+        RTW_CUDA(c, dalloc(pool, &b.top_index, ni));
+        RTW_CUDA(c, dalloc(pool, &b.leaf_mn, n));
+        RTW_CUDA(c, dalloc(pool, &b.leaf_mx, n));
+        RTW_CUDA(c, dalloc(pool, &b.prims_packed, (size_t)2 * n));
+        RTW_CUDA(c, dalloc(pool, &b.prim_ext, n));
+        RTW_CUDA(c, dalloc(pool, &b.leaf_prim, n));
+        RTW_CUDA(c, dalloc(pool, &b.leaf_mat, n));
+        RTW_CUDA(c, dalloc(pool, &b.nodes, (size_t)4 * ni));
+        RTW_CUDA(c, dalloc(pool, &b.top_nodes, (size_t)4 * 3584));
+    }
+    b.max_top = c->opt_top_nodes;
+    uint64_t launches = 0;
+    RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
+    RTW_CUDA(c, lbvh_build(c->stream, b, &launches));
+    RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
+    uint32_t hb[8];
+    RTW_CUDA(c, cudaMemcpyAsync(hb, b.bounds, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
+    c->stats.build_ms = ms;
+    auto dec = [](uint32_t u) { return u2f((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); };
+    for (int i = 0; i < 3; i++) {
+        c->scene_min[i] = dec(hb[i]);
+        c->scene_max[i] = dec(hb[3 + i]);
+    }
+    DScene& sc = c->scene;
+    sc.nodes = b.nodes;
+    sc.top_nodes = b.top_nodes;
+    sc.prims = b.prims_packed;
+    sc.prim_ext = b.prim_ext;
+    sc.leaf_prim = b.leaf_prim;
+    sc.leaf_mat = b.leaf_mat;
+    sc.n_leaves = n;
+    sc.n_internal = ni;
+    sc.n_top = (int)hb[6];
+    sc.root = sc.n_top > 0 ? (RTW_REF_TOP | 0u) : 0u;
+    c->n_internal = ni;
+    RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
+    c->cfg.class_mask = c->class_mask;
+    c->cfg.has_shadow = (sc.n_lights > 0 && sc.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN)));
+    c->accel_built = true;
+    return RTW_OK;
+}

@@ -1,0 +1,82 @@
+// rtw_ctx.h — the opaque context behind the C-ABI (include/rtw.h).
+// Owns every device allocation (the reference's Director owned them and leaked
+// most per-primitive buffers, SURVEY.md §8b "Ownership").
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "../kernels/internal.h"
+
+struct rtw_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string error;
+
+    // ---- scene (device copies) ----
+    bool scene_loaded = false;
+    bool accel_built = false;
+    int n_prims = 0, n_xforms = 0, n_mats = 0;
+    uint32_t class_mask = 0;
+    std::vector<void*> scene_allocs;
+    rtw::BuildBuffers build{};
+    rtw::DScene scene{};
+    rtw::LaunchCfg cfg{};
+    int n_internal = 0;
+    float scene_min[3] = {0, 0, 0}, scene_max[3] = {0, 0, 0};
+
+    // ---- wavefront pool ----
+    std::vector<void*> wave_allocs;
+    rtw::DWave wave{};
+    int wave_capacity = 0;
+    uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
+    cudaEvent_t ring_events[8] = {};
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    cudaEvent_t stage_events[5] = {};
+
+    // ---- last frame ----
+    float4* d_accum = nullptr;          // linear sums of the last rtw_render
+    float4* d_out = nullptr;
+    int frame_pixels = 0;
+    int frame_spp = 0;
+
+    // ---- options ----
+    long long opt_pool_paths = 1 << 21;
+    int opt_top_nodes = 1024;
+    int opt_profile = 0;
+    int opt_lag = 3;
+
+    rtw_stats stats{};
+};
+
+namespace rtw {
+
+inline int fail(rtw_ctx* c, int code, const std::string& msg) {
+    if (c) c->error = msg;
+    return code;
+}
+inline int cuda_fail(rtw_ctx* c, cudaError_t e, const char* what) {
+    return fail(c, RTW_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+#define RTW_CUDA(c, call)                                             \
+    do {                                                              \
+        cudaError_t e__ = (call);                                     \
+        if (e__ != cudaSuccess) return rtw::cuda_fail((c), e__, #call); \
+    } while (0)
+
+template <class T>
+inline cudaError_t dalloc(std::vector<void*>& pool, T** out, size_t count) {
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, sizeof(T) * (count ? count : 1));
+    if (e == cudaSuccess) {
+        pool.push_back(p);
+        *out = reinterpret_cast<T*>(p);
+    }
+    return e;
+}
+inline void dfree_all(std::vector<void*>& pool) {
+    for (void* p : pool) cudaFree(p);
+    pool.clear();
+}
+
+}  // namespace rtw

@@ -1,0 +1,257 @@
+// intersect.h — primitive tests ("candidate" functions) and hit attributes.
+//
+// Restates the reference's intersection programs for a single ray:
+//   geometry/sphere.cu:48-120          sphere
+//   geometry/movingSphere.cu:33-39,61-135   moving sphere (Q24 literal)
+//   shaders/aarectx.cu:8-49, aarecty.cu:8-50, aarectz.cu:9-51   axis-aligned rects
+//   geometry/volumeBox.cu:29-113       constant medium in a box   (Q23)
+//   geometry/volumeSphere.cu:37-127    constant medium in a sphere (Q23)
+// OptiX runtime semantics supplied here: object ray = world→object * world ray,
+// optixReportIntersection accepts iff tmin <= t <= tmax, and the closest hit is
+// the lexicographic minimum of (t, primitive index) — independent of traversal order.
+#pragma once
+#include "layout.h"
+#include "rng.h"
+
+namespace rtw {
+
+// memory policies: read-only global path vs generic (shared-memory staged scene)
+struct MemGlobal {
+    static RTW_HD float4 ld4(const float4* p) {
+#if defined(__CUDA_ARCH__)
+        return __ldg(p);
+#else
+        return *p;
+#endif
+    }
+};
+struct MemGeneric {
+    static RTW_HD float4 ld4(const float4* p) { return *p; }
+};
+
+struct RayW {
+    float3 o, d;
+    float tmin, tmax;
+    float time;     // ray time: motion-transform key interpolation
+    float gather;   // PerRayData::gatherTime: moving-sphere centre
+    uint32_t seed;  // path seed at ray start (constant media, Q23)
+};
+
+// Matrix-motion transform of the moving sphere's instance child
+// (geometry/ioMovingSphere.h:162-182): keys translate(c0), translate(c1) over [0,1].
+RTW_HD float3 motion_translation(float4 a, float4 b, float ray_time) {
+    float f = ray_time;
+    if (f < 0.f) f = 0.f;
+    if (f > 1.f) f = 1.f;
+    return f3(a) * (1.0f - f) + f3(b) * f;
+}
+// geometry/movingSphere.cu:33-39
+RTW_HD float3 moving_center(float4 a, float4 b, float2 times, float time) {
+    if (times.x == times.y) return f3(a);
+    return f3(a) + ((time - times.x) / (times.y - times.x)) * (f3(b) - f3(a));
+}
+
+// geometry/volumeBox.cu:29-52
+RTW_HD bool hit_boundary_box(float3 direction, float3 origin, float3 boxMin, float3 boxMax, float tMin, float tMax, float& rec) {
+    float3 t0 = (boxMin - origin) / direction;
+    float3 t1 = (boxMax - origin) / direction;
+    float temp1 = max3(vmin(t0, t1));
+    float temp2 = min3(vmax(t0, t1));
+    if (temp1 > temp2) return false;
+    if (temp1 < tMax && temp1 > tMin) { rec = temp1; return true; }
+    if (temp2 < tMax && temp2 > tMin) { rec = temp2; return true; }
+    return false;
+}
+// geometry/volumeSphere.cu:37-61
+RTW_HD bool hit_boundary_sphere(float3 direction, float3 origin, float3 center, float radius, float tmin, float tmax, float& rec) {
+    float3 oc = origin - center;
+    float a = dot(direction, direction);
+    float b = dot(oc, direction);
+    float c = dot(oc, oc) - radius * radius;
+    float discriminant = b * b - a * c;
+    if (discriminant < 0.f) return false;
+    float t = (-b - sqrtf(discriminant)) / a;
+    if (t < tmax && t > tmin) { rec = t; return true; }
+    t = (-b + sqrtf(discriminant)) / a;
+    if (t < tmax && t > tmin) { rec = t; return true; }
+    return false;
+}
+
+// Object-space ray of the primitive (a, b, meta).
+template <class Mem>
+RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, const RayW& r, float3& o, float3& d) {
+    const int type = meta_type(meta);
+    o = r.o;
+    d = r.d;
+    if (type == RTW_PRIM_MOVING_SPHERE) {
+        o = r.o - motion_translation(a, b, r.time);
+    } else {
+        const int xf = meta_xform(meta);
+        if (xf >= 0) {
+            const float4* m = sc.xforms + 6 * xf;
+            float4 r0 = Mem::ld4(m), r1 = Mem::ld4(m + 1), r2 = Mem::ld4(m + 2);
+            o = xform_point(r0, r1, r2, r.o);
+            d = xform_vector(r0, r1, r2, r.d);
+        }
+    }
+}
+
+// True (and the accepted distance) iff leaf `leaf` reports an intersection that
+// optixReportIntersection would accept for ray r.
+template <class Mem>
+RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, float& t_out) {
+    const float4 a = Mem::ld4(sc.prims + 2 * leaf);
+    const float4 b = Mem::ld4(sc.prims + 2 * leaf + 1);
+    const uint32_t meta = f2u(b.w);
+    const int type = meta_type(meta);
+    float3 o, d;
+    object_ray<Mem>(sc, a, b, meta, r, o, d);
+    const float tmin = r.tmin, tmax = r.tmax;
+    if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
+        const float k = b.x;
+        float t, pa, pb;
+        if (type == RTW_PRIM_RECT_X) {
+            t = (k - o.x) / d.x;
+            pa = o.y + t * d.y;
+            pb = o.z + t * d.z;
+        } else if (type == RTW_PRIM_RECT_Y) {
+            t = (k - o.y) / d.y;
+            pa = o.x + t * d.x;
+            pb = o.z + t * d.z;
+        } else {
+            t = (k - o.z) / d.z;
+            pa = o.x + t * d.x;
+            pb = o.y + t * d.y;
+        }
+        if (t > tmax || t < tmin) return false;
+        if (pa < a.x || pa > a.y || pb < a.z || pb > a.w) return false;
+        if (!(t >= tmin && t <= tmax)) return false;  // rejects NaN
+        t_out = t;
+        return true;
+    }
+    if (type == RTW_PRIM_SPHERE || type == RTW_PRIM_MOVING_SPHERE) {
+        float3 c = f3(a);
+        if (type == RTW_PRIM_MOVING_SPHERE) {
+#if defined(__CUDA_ARCH__)
+            float2 times = __ldg(sc.prim_ext + leaf);
+#else
+            float2 times = sc.prim_ext[leaf];
+#endif
+            c = moving_center(a, b, times, r.gather);
+        }
+        const float radius = a.w;
+        float3 oc = o - c;
+        float qa = dot(d, d);
+        float qb = dot(oc, d);
+        float qc = dot(oc, oc) - radius * radius;
+        float discriminant = qb * qb - qa * qc;
+        if (discriminant < 0.0f) return false;
+        float sq = sqrtf(discriminant);
+        float t = (-qb - sq) / qa;
+        if (t < tmax && t > tmin) { t_out = t; return true; }
+        t = (-qb + sq) / qa;
+        if (t < tmax && t > tmin) { t_out = t; return true; }
+        return false;
+    }
+    // constant media; EPSILON is `constexpr int` == 0 in the reference (Q23)
+    float hitt1, hitt2, density;
+    if (type == RTW_PRIM_VOLUME_BOX) {
+        density = a.w;
+        float3 bmin = f3(a), bmax = f3(b);
+        if (!hit_boundary_box(d, o, bmin, bmax, -RTW_FLT_MAX, RTW_FLT_MAX, hitt1)) return false;
+        if (!hit_boundary_box(d, o, bmin, bmax, hitt1 + 0, RTW_FLT_MAX, hitt2)) return false;
+    } else {
+        density = b.x;
+        float3 c = f3(a);
+        if (!hit_boundary_sphere(d, o, c, a.w, -RTW_FLT_MAX, RTW_FLT_MAX, hitt1)) return false;
+        if (!hit_boundary_sphere(d, o, c, a.w, hitt1 + 0, RTW_FLT_MAX, hitt2)) return false;
+    }
+    if (hitt1 < tmin) hitt1 = tmin;
+    if (hitt2 > tmax) hitt2 = tmax;
+    if (hitt1 >= hitt2) return false;
+    if (hitt1 < 0.f) hitt1 = 0.f;
+#if defined(__CUDA_ARCH__)
+    const int prim = __ldg(sc.leaf_prim + leaf);
+#else
+    const int prim = sc.leaf_prim[leaf];
+#endif
+    uint32_t st = medium_state(r.seed, (uint32_t)prim);
+    float u = (type == RTW_PRIM_VOLUME_BOX) ? randf(st) : rnd(st);  // volumeBox.cu:79 / volumeSphere.cu:93
+    float hitDistance = -(1.f / density) * logf(u);
+    float hitt = hitt1 + (hitDistance / length(d));
+    if (!(hitt >= tmin && hitt <= tmax)) return false;
+    t_out = hitt;
+    return true;
+}
+
+struct HitAttr {    // HitRecord, lib/raydata.cuh:117-124
+    float3 point;
+    float3 normal;
+    float u, v;
+};
+
+// geometry/sphere.cu:24-32
+RTW_HD void get_sphere_uv(float3 p, float& u, float& v) {
+    float phi = atan2f(p.z, p.x);
+    float theta = asinf(p.y);
+    u = 1 - (phi + RTW_PI) / (2.f * RTW_PI);
+    v = (theta + RTW_PIO2) / RTW_PI;
+}
+
+// Attributes of the winning intersection program (normal, uv, world point).
+template <class Mem>
+RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float t, bool want_uv, HitAttr& h) {
+    const float4 a = Mem::ld4(sc.prims + 2 * leaf);
+    const float4 b = Mem::ld4(sc.prims + 2 * leaf + 1);
+    const uint32_t meta = f2u(b.w);
+    const int type = meta_type(meta);
+    float3 o, d;
+    object_ray<Mem>(sc, a, b, meta, r, o, d);
+    const int xf = (type == RTW_PRIM_MOVING_SPHERE) ? -1 : meta_xform(meta);
+    float4 w0, w1, w2, q0, q1, q2;  // world→object rows, object→world rows
+    if (xf >= 0) {
+        const float4* m = sc.xforms + 6 * xf;
+        w0 = Mem::ld4(m); w1 = Mem::ld4(m + 1); w2 = Mem::ld4(m + 2);
+        q0 = Mem::ld4(m + 3); q1 = Mem::ld4(m + 4); q2 = Mem::ld4(m + 5);
+    }
+    float3 pobj = o + t * d;
+    float3 point;
+    if (type == RTW_PRIM_MOVING_SPHERE) point = pobj + motion_translation(a, b, r.time);
+    else point = (xf >= 0) ? xform_point(q0, q1, q2, pobj) : pobj;
+    h.point = point;
+    h.u = 0.f;
+    h.v = 0.f;
+    if (type == RTW_PRIM_SPHERE || type == RTW_PRIM_MOVING_SPHERE) {
+        // Q21: world-space point minus OBJECT-space centre, not normalised
+        float3 c = f3(a);
+        if (type == RTW_PRIM_MOVING_SPHERE) {
+#if defined(__CUDA_ARCH__)
+            float2 times = __ldg(sc.prim_ext + leaf);
+#else
+            float2 times = sc.prim_ext[leaf];
+#endif
+            c = moving_center(a, b, times, r.gather);
+        }
+        float3 n = (point - c) / a.w;
+        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
+        h.normal = n;
+        if (want_uv) get_sphere_uv(n, h.u, h.v);
+    } else if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
+        float pa, pb;
+        float3 n;
+        if (type == RTW_PRIM_RECT_X) { pa = o.y + t * d.y; pb = o.z + t * d.z; n = f3(1.f, 0.f, 0.f); }
+        else if (type == RTW_PRIM_RECT_Y) { pa = o.x + t * d.x; pb = o.z + t * d.z; n = f3(0.f, 1.f, 0.f); }
+        else { pa = o.x + t * d.x; pb = o.y + t * d.y; n = f3(0.f, 0.f, 1.f); }
+        if (meta_flip(meta)) n = -n;
+        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
+        h.normal = normalize(n);
+        h.u = (pa - a.x) / (a.y - a.x);
+        h.v = (pb - a.z) / (a.w - a.z);
+    } else {  // volumes: normal (1,0,0), uv 0 (volumeBox.cu:88-93, volumeSphere.cu:99-105)
+        float3 n = f3(1.f, 0.f, 0.f);
+        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
+        h.normal = normalize(n);
+    }
+}
+
+}  // namespace rtw

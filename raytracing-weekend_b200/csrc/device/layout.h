@@ -1,0 +1,125 @@
+// layout.h — HBM data layout of the scene, the LBVH and the wavefront state.
+// (DESIGN.md "Data layout in HBM" describes every array and its bytes/unit.)
+#pragma once
+#include "vec.h"
+#include "../../../include/rtw.h"
+
+namespace rtw {
+
+// ---- child reference of a BVH node ---------------------------------------
+// bit 31: leaf (low 30 bits = leaf index, i.e. position in Morton order)
+// bit 30: node lives in the shared-memory "top" table (low bits = top index)
+// else  : index into the global node array
+#define RTW_REF_LEAF 0x80000000u
+#define RTW_REF_TOP  0x40000000u
+#define RTW_REF_MASK 0x3fffffffu
+#define RTW_REF_NONE 0xffffffffu
+
+// ---- primitive record: 2 x float4 per leaf, stored in leaf (Morton) order ----
+//   SPHERE         a = c.xyz r          b = -  -  -  meta
+//   MOVING_SPHERE  a = c0.xyz r         b = c1.xyz   meta     (+ prim_ext: time0 time1)
+//   RECT_X/Y/Z     a = a0 a1 b0 b1      b = k  -  -  meta
+//   VOLUME_BOX     a = min.xyz density  b = max.xyz  meta
+//   VOLUME_SPHERE  a = c.xyz r          b = density - - meta
+// meta (bit pattern of b.w): type[0:3) flip[3] material-type[4:7) (transform+1)[7:32)
+RTW_HD uint32_t meta_pack(int type, int flip, int mattype, int xform) {
+    return (uint32_t)type | ((uint32_t)(flip & 1) << 3) | ((uint32_t)mattype << 4) | ((uint32_t)(xform + 1) << 7);
+}
+RTW_HD int meta_type(uint32_t m) { return (int)(m & 7u); }
+RTW_HD int meta_flip(uint32_t m) { return (int)((m >> 3) & 1u); }
+RTW_HD int meta_mattype(uint32_t m) { return (int)((m >> 4) & 7u); }
+RTW_HD int meta_xform(uint32_t m) { return (int)(m >> 7) - 1; }  // -1 = identity
+
+#define RTW_MAX_LIGHTS 8
+
+struct DLight {            // LightDefinition (reference lib/raydata.cuh:32-49)
+    float3 normal;
+    float  area;
+    float3 emission;
+    float  pad;
+};
+
+struct DImage {
+    const uchar4* texels;  // RGBA8, row 0 = v == 0
+    int width, height;
+};
+
+// Read-only scene, passed to kernels by value (lives in the constant bank).
+struct DScene {
+    // LBVH
+    const float4* nodes;        // 4 float4 (64 B) per internal node, see lbvh.h
+    const float4* top_nodes;    // n_top nodes re-indexed breadth-first for shared-memory staging
+    const float4* prims;        // 2 float4 (32 B) per leaf
+    const float2* prim_ext;     // per leaf: (time0, time1) of a moving sphere
+    const int*    leaf_prim;    // leaf → index into rtw_scene_desc::prims
+    const int*    leaf_mat;     // leaf → material index
+    const float4* xforms;       // 6 float4 per transform: world→object rows 0-2, object→world rows 0-2
+    uint32_t root;              // child reference of the root
+    int n_leaves, n_internal, n_top;
+    int has_media;              // scene contains constant media (ray seed needed in traversal)
+    int has_motion;             // scene contains moving spheres (gather time needed by shadow rays)
+    int has_images;             // scene contains image textures (sphere uv needed)
+    // shading tables
+    const float4* mats;         // 1 float4 per material: (type, texture, param, -) as bit patterns
+    const float4* texs;         // 2 float4 per texture: (type, r, g, b) (odd, even, scale, table/image index)
+    const float4* perlin_vec;   // 256 float4 per Perlin table
+    const int*    perlin_perm;  // 768 ints per Perlin table: perm_x, perm_y, perm_z
+    const DImage* images;
+    // lights (reference SysParamter: lights, numLights, pdf; Director.cpp:523-549)
+    int n_lights;
+    int sky_light;
+    int has_light_rect;
+    int rect_axis;
+    float rect_a0, rect_a1, rect_b0, rect_b1, rect_k;
+    DLight lights[RTW_MAX_LIGHTS];
+    // camera (shaders/sysparameter.h:44-56)
+    float3 cam_origin, cam_u, cam_v, cam_ll, cam_horizontal, cam_vertical;
+    float cam_lens_radius, cam_time0, cam_time1;
+};
+
+// ---- wavefront state: structure of arrays over P path slots ---------------
+// bytes per slot: ray 32 + hit 8 + throughput/seed 16 + radiance/pixel 16 + misc 8 = 80
+#define RTW_ST_EMPTY 0u
+#define RTW_ST_ALIVE 1u
+#define RTW_ST_DEAD  2u     // finished: radiance waits to be flushed by k_logic
+
+// shading queue classes ("one BSDF per warp")
+#define RTW_Q_LAMBERTIAN 0
+#define RTW_Q_METAL      1
+#define RTW_Q_DIELECTRIC 2
+#define RTW_Q_ISOTROPIC  3
+#define RTW_Q_TERMINAL   4   // miss, diffuse light, normal material: path ends
+#define RTW_Q_COUNT      5
+
+// counters[] layout (uint32 unless noted)
+#define RTW_C_QUEUE0     0                 // RTW_Q_COUNT queue lengths
+#define RTW_C_SHADOW     5                 // shadow queue length
+#define RTW_C_ALIVE      6                 // live paths after the last k_logic
+#define RTW_C_PAD        7
+#define RTW_C_NEXT_LO    8                 // uint64 next sample ordinal (two words)
+#define RTW_C_RAYS_LO    10                // uint64 closest-hit rays traced
+#define RTW_C_SHRAYS_LO  12                // uint64 shadow rays traced
+#define RTW_C_PATHS_LO   14                // uint64 paths flushed
+#define RTW_C_WORDS      16
+
+struct DWave {
+    float4* ray_o;      // origin.xyz, ray time
+    float4* ray_d;      // direction.xyz, gather time
+    uint2*  hit;        // (t bits, leaf index or RTW_REF_NONE)
+    float4* thr;        // throughput.xyz, path seed bits
+    float4* rad;        // radiance sum .xyz, pixel index bits
+    uint2*  misc;       // (depth | state << 8, ray-time seed)
+    uint32_t* queue;    // RTW_Q_COUNT * P slot indices
+    float4* sh_o;       // shadow queue: origin.xyz, tmax
+    float4* sh_d;       //               direction.xyz, slot bits
+    float4* sh_c;       //               contribution.xyz, path seed bits
+    uint32_t* counters; // RTW_C_WORDS words
+    float4* accum;      // Nx*Ny linear radiance sums (rgb) + sample count (w)
+    int P;
+    int Nx, Ny;
+    int max_depth;
+    int sample_first, sample_stride;
+    unsigned long long total;   // Nx*Ny*sample_count sample ordinals to issue
+};
+
+}  // namespace rtw

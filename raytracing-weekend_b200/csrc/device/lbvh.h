@@ -1,0 +1,195 @@
+// lbvh.h — per-thread bodies of the GPU LBVH builder.
+//
+// Replaces every optixAccelBuild call site of the reference (one single-primitive
+// GAS per primitive plus one IAS: geometry/ioSphere.h:45-92, ioAARect.h:96,
+// ioMovingSphere.h:135, ioVolumeBox.h:69, ioVolumeSphere.h:69,
+// ioGeometryGroup.h:160-225) by ONE two-child LBVH over all primitives:
+//   world AABB per primitive → scene bounds → 63-bit Morton code of the centroid
+//   → stable radix sort → Karras 2012 hierarchy → bottom-up refit.
+// Primitive AABBs follow the reference's bounds functions (cited below) and are
+// padded by 2^-21 of the largest |coordinate| so that the slab test can never
+// cull a primitive whose intersection test would accept the ray.
+#pragma once
+#include "layout.h"
+
+namespace rtw {
+
+struct Box3 {
+    float3 mn, mx;
+};
+
+RTW_HD Box3 prim_object_aabb(const rtw_prim& p) {
+    Box3 b;
+    switch (p.type) {
+    case RTW_PRIM_SPHERE: {  // geometry/ioSphere.h:25-34
+        float3 c = f3(p.v[0], p.v[1], p.v[2]);
+        b.mn = c - p.v[3];
+        b.mx = c + p.v[3];
+        break;
+    }
+    case RTW_PRIM_MOVING_SPHERE: {  // geometry/ioMovingSphere.h:46-72, swept by the motion keys (Q24)
+        float3 c0 = f3(p.v[0], p.v[1], p.v[2]), c1 = f3(p.v[4], p.v[5], p.v[6]);
+        float r = p.v[3];
+        float3 lo = vmin(c0 - r, c1 - r), hi = vmax(c0 + r, c1 + r);
+        b.mn = vmin(lo + c0, lo + c1);
+        b.mx = vmax(hi + c0, hi + c1);
+        break;
+    }
+    case RTW_PRIM_RECT_X:  // geometry/ioAARect.h:128-154
+        b.mn = f3(p.v[4] - 0.0001f, p.v[0], p.v[2]);
+        b.mx = f3(p.v[4] + 0.0001f, p.v[1], p.v[3]);
+        break;
+    case RTW_PRIM_RECT_Y:
+        b.mn = f3(p.v[0], p.v[4] - 0.0001f, p.v[2]);
+        b.mx = f3(p.v[1], p.v[4] + 0.0001f, p.v[3]);
+        break;
+    case RTW_PRIM_RECT_Z:
+        b.mn = f3(p.v[0], p.v[2], p.v[4] - 0.0001f);
+        b.mx = f3(p.v[1], p.v[3], p.v[4] + 0.0001f);
+        break;
+    case RTW_PRIM_VOLUME_BOX:  // geometry/ioVolumeBox.h:76-84
+        b.mn = f3(p.v[0], p.v[1], p.v[2]) - 0.0001f;
+        b.mx = f3(p.v[3], p.v[4], p.v[5]) + 0.0001f;
+        break;
+    default: {  // geometry/ioVolumeSphere.h:76-82
+        float3 c = f3(p.v[0], p.v[1], p.v[2]);
+        float r = fabsf(p.v[3]);
+        b.mn = c - r;
+        b.mx = c + r;
+        break;
+    }
+    }
+    return b;
+}
+
+// World-space, padded AABB of primitive p (instance transform applied to the 8 corners).
+RTW_HD Box3 prim_world_aabb(const rtw_prim& p, const rtw_transform* xforms) {
+    Box3 b = prim_object_aabb(p);
+    if (p.type != RTW_PRIM_MOVING_SPHERE && p.transform >= 0) {
+        const float* m = xforms[p.transform].o2w;
+        const float4 r0 = make_float4(m[0], m[1], m[2], m[3]);
+        const float4 r1 = make_float4(m[4], m[5], m[6], m[7]);
+        const float4 r2 = make_float4(m[8], m[9], m[10], m[11]);
+        Box3 w;
+        w.mn = f3(RTW_FLT_MAX);
+        w.mx = f3(-RTW_FLT_MAX);
+        for (int i = 0; i < 8; i++) {
+            float3 c = f3((i & 1) ? b.mx.x : b.mn.x, (i & 2) ? b.mx.y : b.mn.y, (i & 4) ? b.mx.z : b.mn.z);
+            float3 q = xform_point(r0, r1, r2, c);
+            w.mn = vmin(w.mn, q);
+            w.mx = vmax(w.mx, q);
+        }
+        b = w;
+    }
+    float m = fmaxf(fmaxf(fmaxf(fabsf(b.mn.x), fabsf(b.mn.y)), fabsf(b.mn.z)),
+                    fmaxf(fmaxf(fabsf(b.mx.x), fabsf(b.mx.y)), fabsf(b.mx.z)));
+    float pad = m * 4.76837158203125e-7f;  // 2^-21
+    b.mn = b.mn - pad;
+    b.mx = b.mx + pad;
+    return b;
+}
+
+RTW_HD unsigned long long expand21(uint32_t v) {
+    unsigned long long x = v & 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+RTW_HD uint32_t quant21(float c, float lo, float ext) {
+    float n = (ext > 0.f) ? (c - lo) / ext : 0.f;
+    float q = n * 2097152.0f;
+    if (!(q >= 0.f)) q = 0.f;
+    if (q > 2097151.0f) q = 2097151.0f;
+    return (uint32_t)q;
+}
+RTW_HD unsigned long long morton63(const Box3& b, float3 lo, float3 ext) {
+    float3 c = (b.mn + b.mx) * 0.5f;
+    return (expand21(quant21(c.x, lo.x, ext.x)) << 2) | (expand21(quant21(c.y, lo.y, ext.y)) << 1) |
+           expand21(quant21(c.z, lo.z, ext.z));
+}
+
+RTW_HD int clz64(unsigned long long x) {
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+RTW_HD int clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int)x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+
+// common-prefix length of keys i and j, ties broken by index (Karras 2012, §4)
+RTW_HD int lbvh_delta(const unsigned long long* k, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long a = k[i], b = k[j];
+    if (a == b) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
+    return clz64(a ^ b);
+}
+
+// Internal node i of the hierarchy over n >= 2 sorted keys.  Child refs use the
+// download convention: >= 0 internal node, < 0 → leaf ~ref.
+RTW_HD void karras_node(const unsigned long long* k, int n, int i, int& left, int& right) {
+    const int d = (lbvh_delta(k, n, i, i + 1) - lbvh_delta(k, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = lbvh_delta(k, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(k, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lbvh_delta(k, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = lbvh_delta(k, n, i, j);
+    int sp = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (lbvh_delta(k, n, i, i + (sp + t) * d) > dnode) sp += t;
+    } while (t > 1);
+    const int gamma = i + sp * d + (d < 0 ? d : 0);
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    left = (lo == gamma) ? ~gamma : gamma;
+    right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+}
+
+// Convert a download-convention ref into the traversal encoding of layout.h.
+RTW_HD uint32_t encode_ref(int ref) { return ref < 0 ? (RTW_REF_LEAF | (uint32_t)(~ref)) : (uint32_t)ref; }
+
+// Pack primitive p (material type mt) into its two-float4 leaf record.
+RTW_HD void pack_prim(const rtw_prim& p, int mattype, float4& a, float4& b, float2& ext) {
+    const float meta = u2f(meta_pack(p.type, p.flip, mattype, p.type == RTW_PRIM_MOVING_SPHERE ? -1 : p.transform));
+    ext = make_float2(0.f, 0.f);
+    switch (p.type) {
+    case RTW_PRIM_SPHERE:
+        a = make_float4(p.v[0], p.v[1], p.v[2], p.v[3]);
+        b = make_float4(0.f, 0.f, 0.f, meta);
+        break;
+    case RTW_PRIM_MOVING_SPHERE:
+        a = make_float4(p.v[0], p.v[1], p.v[2], p.v[3]);
+        b = make_float4(p.v[4], p.v[5], p.v[6], meta);
+        ext = make_float2(p.v[7], p.v[8]);
+        break;
+    case RTW_PRIM_RECT_X:
+    case RTW_PRIM_RECT_Y:
+    case RTW_PRIM_RECT_Z:
+        a = make_float4(p.v[0], p.v[1], p.v[2], p.v[3]);
+        b = make_float4(p.v[4], 0.f, 0.f, meta);
+        break;
+    case RTW_PRIM_VOLUME_BOX:
+        a = make_float4(p.v[0], p.v[1], p.v[2], p.v[6]);
+        b = make_float4(p.v[3], p.v[4], p.v[5], meta);
+        break;
+    default:
+        a = make_float4(p.v[0], p.v[1], p.v[2], p.v[3]);
+        b = make_float4(p.v[4], 0.f, 0.f, meta);
+        break;
+    }
+}
+
+}  // namespace rtw

@@ -1,0 +1,150 @@
+// traverse.h — stack-based traversal of the two-child LBVH.
+//
+// Replaces the driver-internal optixTraverse of the reference
+// (raygen/raygen.cu:41-54 closest hit; shaders/closehit.cu:27-40 any hit with
+// OPTIX_RAY_FLAG_TERMINATE_ON_FIRST_HIT).  Node = 64 B = 4 float4:
+//   n0 = lmin.x lmin.y lmin.z lmax.x
+//   n1 = lmax.y lmax.z rmin.x rmin.y
+//   n2 = rmin.z rmax.x rmax.y rmax.z
+//   n3 = left-ref right-ref parent -      (bit patterns, see layout.h)
+// The first n_top nodes (breadth-first) are staged in shared memory by the
+// kernels; `top` points at that copy (nullptr → everything from global memory).
+#pragma once
+#include "intersect.h"
+
+namespace rtw {
+
+#define RTW_STACK 96
+
+struct TravStats {
+    uint32_t nodes;
+    uint32_t prims;
+};
+
+template <class Mem>
+RTW_HD void fetch_node(const DScene& sc, const float4* top, uint32_t ref, float4& n0, float4& n1, float4& n2, float4& n3) {
+    if (ref & RTW_REF_TOP) {
+        const float4* p = top + 4 * (ref & RTW_REF_MASK);
+        n0 = p[0]; n1 = p[1]; n2 = p[2]; n3 = p[3];
+    } else {
+        const float4* p = sc.nodes + 4 * (size_t)ref;
+        n0 = Mem::ld4(p); n1 = Mem::ld4(p + 1); n2 = Mem::ld4(p + 2); n3 = Mem::ld4(p + 3);
+    }
+}
+
+// Conservative slab test of both children against [tmin, limit].
+// t = fma(bound, 1/d, -o/d); NaNs (0 * inf) drop out of fminf/fmaxf, which only
+// widens the interval.  The far side is padded by 2 ulp-ish (Ize 2013).
+struct SlabRay {
+    float3 inv, ood;
+};
+RTW_HD SlabRay make_slab_ray(const RayW& r) {
+    SlabRay s;
+    s.inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    s.ood = f3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
+    return s;
+}
+RTW_HD bool slab_test(const SlabRay& s, float minx, float miny, float minz, float maxx, float maxy, float maxz,
+                      float tmin, float limit, float& tnear) {
+    float x0 = fmaf(minx, s.inv.x, -s.ood.x), x1 = fmaf(maxx, s.inv.x, -s.ood.x);
+    float y0 = fmaf(miny, s.inv.y, -s.ood.y), y1 = fmaf(maxy, s.inv.y, -s.ood.y);
+    float z0 = fmaf(minz, s.inv.z, -s.ood.z), z1 = fmaf(maxz, s.inv.z, -s.ood.z);
+    float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+    float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), limit));
+    tnear = tn;
+    return tn <= tf * 1.0000004f;
+}
+
+RTW_HD int leaf_prim_of(const DScene& sc, uint32_t leaf) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(sc.leaf_prim + leaf);
+#else
+    return sc.leaf_prim[leaf];
+#endif
+}
+
+// Closest hit: lexicographic minimum of (t, primitive index).
+template <class Mem, bool kStats>
+RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r, float& t_best, uint32_t& leaf_best,
+                             TravStats* stats) {
+    const SlabRay sr = make_slab_ray(r);
+    uint32_t stack[RTW_STACK];
+    int sp = 0;
+    uint32_t cur = sc.root;
+    bool found = false;
+    float tb = r.tmax;
+    uint32_t lb = RTW_REF_NONE;
+    for (;;) {
+        if (cur & RTW_REF_LEAF) {
+            const uint32_t leaf = cur & RTW_REF_MASK;
+            float t;
+            if (kStats) stats->prims++;
+            if (prim_candidate<Mem>(sc, leaf, r, t)) {
+                bool better = !found || t < tb;
+                if (!better && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);
+                if (better) {
+                    found = true;
+                    tb = t;
+                    lb = leaf;
+                }
+            }
+        } else {
+            float4 n0, n1, n2, n3;
+            fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
+            if (kStats) stats->nodes++;
+            float tl, tr;
+            const bool hl = slab_test(sr, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, r.tmin, tb, tl);
+            const bool hr = slab_test(sr, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.tmin, tb, tr);
+            const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
+            if (hl && hr) {
+                const bool left_first = tl <= tr;
+                if (sp < RTW_STACK) stack[sp++] = left_first ? cr : cl;
+                cur = left_first ? cl : cr;
+                continue;
+            }
+            if (hl) { cur = cl; continue; }
+            if (hr) { cur = cr; continue; }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    t_best = tb;
+    leaf_best = lb;
+    return found;
+}
+
+// Any hit (shadow rays): true iff some primitive reports an accepted hit in [tmin, tmax].
+template <class Mem, bool kStats>
+RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, TravStats* stats) {
+    const SlabRay sr = make_slab_ray(r);
+    uint32_t stack[RTW_STACK];
+    int sp = 0;
+    uint32_t cur = sc.root;
+    for (;;) {
+        if (cur & RTW_REF_LEAF) {
+            float t;
+            if (kStats) stats->prims++;
+            if (prim_candidate<Mem>(sc, cur & RTW_REF_MASK, r, t)) return true;
+        } else {
+            float4 n0, n1, n2, n3;
+            fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
+            if (kStats) stats->nodes++;
+            float tl, tr;
+            const bool hl = slab_test(sr, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, r.tmin, r.tmax, tl);
+            const bool hr = slab_test(sr, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.tmin, r.tmax, tr);
+            const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
+            if (hl && hr) {
+                if (sp < RTW_STACK) stack[sp++] = cr;
+                cur = cl;
+                continue;
+            }
+            if (hl) { cur = cl; continue; }
+            if (hr) { cur = cr; continue; }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    return false;
+}
+
+}  // namespace rtw

@@ -1,0 +1,71 @@
+// internal.h — launch functions shared between the kernel translation units and
+// the C-ABI implementation (api/rtw_api.cu).  Not part of the public boundary.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../device/layout.h"
+
+namespace rtw {
+
+// ---- radix sort (kernels/sort.cu) -----------------------------------------
+// Stable LSD radix sort of (64-bit key, 32-bit value) pairs, 8 passes of 8 bits.
+// keys/vals are ping-pong buffers of n elements each; the sorted result ends in
+// keys[0]/vals[0].  hist must hold 256 * sort_num_blocks(n) + 1024 uint32.
+int  sort_num_blocks(int n);
+cudaError_t sort_pairs(cudaStream_t s, unsigned long long* keys[2], uint32_t* vals[2], int n, uint32_t* hist,
+                       uint64_t* launches);
+
+// ---- LBVH build (kernels/lbvh.cu) -------------------------------------------
+struct BuildBuffers {
+    // inputs (device copies of the C-ABI scene arrays)
+    const rtw_prim* prims;          // n
+    const rtw_transform* xforms;    // may be null
+    const rtw_material* mats_raw;   // for the material type in the leaf meta word
+    int n;
+    // scratch
+    float4* box_mn;                 // n, prim order
+    float4* box_mx;
+    uint32_t* bounds;               // 6 order-preserving encoded floats + n_top word
+    unsigned long long* keys[2];
+    uint32_t* vals[2];
+    uint32_t* hist;
+    int* parent;                    // n_internal
+    int* leaf_parent;               // n
+    int* flags;                     // n_internal
+    int* top_index;                 // n_internal
+    // outputs
+    float4* leaf_mn;                // n, leaf order
+    float4* leaf_mx;
+    float4* prims_packed;           // 2n
+    float2* prim_ext;               // n
+    int* leaf_prim;                 // n
+    int* leaf_mat;                  // n
+    float4* nodes;                  // 4 * n_internal
+    float4* top_nodes;              // 4 * max_top
+    int max_top;
+};
+cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches);
+
+// ---- wavefront (kernels/wavefront.cu) --------------------------------------
+struct LaunchCfg {
+    int grid_logic, grid_traverse, grid_shade, grid_shadow;
+    int block;
+    size_t smem_top;        // bytes of shared memory for the staged top nodes
+    uint32_t class_mask;    // which shading queues the scene can populate
+    bool has_shadow;        // scene has lights → NEE stage runs
+};
+cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
+// One wavefront iteration: reset counters, logic, traverse, shade*, shadow.
+cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
+                                uint64_t* launches, cudaEvent_t* stage_events /* 5 or null */);
+cudaError_t wavefront_init(cudaStream_t s, const DWave& w, uint64_t* launches);
+cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
+
+// ---- test hooks --------------------------------------------------------------
+cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg, const rtw_ray* rays, int n,
+                         rtw_hit* hits, int32_t* occluded, uint64_t* launches);
+cudaError_t launch_rng_stream(cudaStream_t s, uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out,
+                              uint32_t* lcg_out, float* rnd_out, uint32_t* xs_out, float* randf_out);
+cudaError_t launch_camera_rays(cudaStream_t s, const DScene& sc, const DWave& w, int sample, rtw_ray* rays_out);
+
+}  // namespace rtw

@@ -1,0 +1,252 @@
+// lbvh.cu — GPU LBVH build (replaces optixAccelBuild).
+//
+//   k_prim_aabb   world AABB per primitive + scene bounds (warp shuffle + atomics)
+//   k_morton      63-bit Morton code of the AABB centroid
+//   sort_pairs    stable radix sort (kernels/sort.cu)
+//   k_pack_leaves leaf-ordered primitive records (32 B), leaf boxes, ids
+//   k_karras      Karras 2012 hierarchy, one thread per internal node
+//   k_refit       bottom-up AABB refit with atomic arrival flags
+//   k_build_top   breadth-first copy of the top nodes for shared-memory staging
+// All kernels are HBM-bound streaming passes; bytes per primitive are listed in
+// DESIGN.md ("LBVH build").
+#include "internal.h"
+#include "../device/lbvh.h"
+
+namespace rtw {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// order-preserving float → uint map for atomicMin/atomicMax
+__device__ __forceinline__ uint32_t enc_f(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float dec_f(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__global__ void k_bounds_init(uint32_t* bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;        // min
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = 0u;            // max
+    else if (threadIdx.x < 8) bounds[threadIdx.x] = 0u;            // [6] = n_top
+}
+
+__global__ void __launch_bounds__(kThreads) k_prim_aabb(const rtw_prim* __restrict__ prims,
+                                                         const rtw_transform* __restrict__ xforms, int n,
+                                                         float4* __restrict__ box_mn, float4* __restrict__ box_mx,
+                                                         uint32_t* __restrict__ bounds) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float3 mn = f3(RTW_FLT_MAX), mx = f3(-RTW_FLT_MAX);
+    if (i < n) {
+        const Box3 b = prim_world_aabb(prims[i], xforms);
+        box_mn[i] = make_float4(b.mn.x, b.mn.y, b.mn.z, 0.f);
+        box_mx[i] = make_float4(b.mx.x, b.mx.y, b.mx.z, 0.f);
+        mn = b.mn;
+        mx = b.mx;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn.x = fminf(mn.x, __shfl_xor_sync(0xffffffffu, mn.x, o));
+        mn.y = fminf(mn.y, __shfl_xor_sync(0xffffffffu, mn.y, o));
+        mn.z = fminf(mn.z, __shfl_xor_sync(0xffffffffu, mn.z, o));
+        mx.x = fmaxf(mx.x, __shfl_xor_sync(0xffffffffu, mx.x, o));
+        mx.y = fmaxf(mx.y, __shfl_xor_sync(0xffffffffu, mx.y, o));
+        mx.z = fmaxf(mx.z, __shfl_xor_sync(0xffffffffu, mx.z, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(bounds + 0, enc_f(mn.x));
+        atomicMin(bounds + 1, enc_f(mn.y));
+        atomicMin(bounds + 2, enc_f(mn.z));
+        atomicMax(bounds + 3, enc_f(mx.x));
+        atomicMax(bounds + 4, enc_f(mx.y));
+        atomicMax(bounds + 5, enc_f(mx.z));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_morton(const float4* __restrict__ box_mn, const float4* __restrict__ box_mx,
+                                                      int n, const uint32_t* __restrict__ bounds,
+                                                      unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float3 lo = f3(dec_f(bounds[0]), dec_f(bounds[1]), dec_f(bounds[2]));
+    const float3 hi = f3(dec_f(bounds[3]), dec_f(bounds[4]), dec_f(bounds[5]));
+    Box3 b;
+    b.mn = f3(box_mn[i]);
+    b.mx = f3(box_mx[i]);
+    keys[i] = morton63(b, lo, hi - lo);
+    vals[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(kThreads) k_pack_leaves(const rtw_prim* __restrict__ prims,
+                                                           const rtw_material* __restrict__ mats, int n,
+                                                           const uint32_t* __restrict__ vals,
+                                                           const float4* __restrict__ box_mn, const float4* __restrict__ box_mx,
+                                                           float4* __restrict__ leaf_mn, float4* __restrict__ leaf_mx,
+                                                           float4* __restrict__ packed, float2* __restrict__ ext,
+                                                           int* __restrict__ leaf_prim, int* __restrict__ leaf_mat) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int pi = (int)vals[j];
+    const rtw_prim p = prims[pi];
+    float4 a, b;
+    float2 e;
+    pack_prim(p, mats[p.material].type, a, b, e);
+    packed[2 * j] = a;
+    packed[2 * j + 1] = b;
+    ext[j] = e;
+    leaf_prim[j] = pi;
+    leaf_mat[j] = p.material;
+    leaf_mn[j] = box_mn[pi];
+    leaf_mx[j] = box_mx[pi];
+}
+
+__global__ void __launch_bounds__(kThreads) k_karras(const unsigned long long* __restrict__ keys, int n,
+                                                      float4* __restrict__ nodes, int* __restrict__ parent,
+                                                      int* __restrict__ leaf_parent, int* __restrict__ flags,
+                                                      int* __restrict__ top_index) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int left, right;
+    karras_node(keys, n, i, left, right);
+    if (left < 0) leaf_parent[~left] = i; else parent[left] = i;
+    if (right < 0) leaf_parent[~right] = i; else parent[right] = i;
+    if (i == 0) parent[0] = -1;
+    flags[i] = 0;
+    top_index[i] = -1;
+    // children now, boxes at refit; n3.z keeps the download-convention refs recoverable
+    nodes[4 * i + 3] = make_float4(__uint_as_float(encode_ref(left)), __uint_as_float(encode_ref(right)), 0.f, 0.f);
+}
+
+// One-leaf scene: node 0 = (leaf 0, unreachable point box at +FLT_MAX).  An inverted
+// "empty" box would not work: the slab test symmetrises min/max per axis.
+__global__ void k_single_leaf(const float4* leaf_mn, const float4* leaf_mx, float4* nodes, int* parent, int* top_index) {
+    const float4 mn = leaf_mn[0], mx = leaf_mx[0];
+    nodes[0] = make_float4(mn.x, mn.y, mn.z, mx.x);
+    nodes[1] = make_float4(mx.y, mx.z, RTW_FLT_MAX, RTW_FLT_MAX);
+    nodes[2] = make_float4(RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX);
+    nodes[3] = make_float4(__uint_as_float(RTW_REF_LEAF | 0u), __uint_as_float(RTW_REF_LEAF | 0u), 0.f, 0.f);
+    parent[0] = -1;
+    top_index[0] = -1;
+}
+
+__device__ __forceinline__ void child_box(uint32_t ref, const float4* leaf_mn, const float4* leaf_mx,
+                                          const float4* nodes, float3& mn, float3& mx) {
+    if (ref & RTW_REF_LEAF) {
+        const uint32_t l = ref & RTW_REF_MASK;
+        mn = f3(leaf_mn[l]);
+        mx = f3(leaf_mx[l]);
+    } else {
+        // written by another thread before its atomic arrival: bypass L1
+        const float4 n0 = __ldcg(nodes + 4 * ref), n1 = __ldcg(nodes + 4 * ref + 1), n2 = __ldcg(nodes + 4 * ref + 2);
+        mn = vmin(f3(n0.x, n0.y, n0.z), f3(n1.z, n1.w, n2.x));
+        mx = vmax(f3(n0.w, n1.x, n1.y), f3(n2.y, n2.z, n2.w));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_refit(int n, const int* __restrict__ leaf_parent, const int* __restrict__ parent,
+                                                     int* flags, const float4* __restrict__ leaf_mn,
+                                                     const float4* __restrict__ leaf_mx, float4* nodes) {
+    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= n) return;
+    int cur = leaf_parent[leaf];
+    while (cur >= 0) {
+        if (atomicAdd(flags + cur, 1) == 0) return;  // first arrival stops, second computes
+        __threadfence();
+        const float4 n3 = nodes[4 * cur + 3];
+        float3 lmn, lmx, rmn, rmx;
+        child_box(__float_as_uint(n3.x), leaf_mn, leaf_mx, nodes, lmn, lmx);
+        child_box(__float_as_uint(n3.y), leaf_mn, leaf_mx, nodes, rmn, rmx);
+        nodes[4 * cur + 0] = make_float4(lmn.x, lmn.y, lmn.z, lmx.x);
+        nodes[4 * cur + 1] = make_float4(lmx.y, lmx.z, rmn.x, rmn.y);
+        nodes[4 * cur + 2] = make_float4(rmn.z, rmx.x, rmx.y, rmx.z);
+        __threadfence();
+        cur = parent[cur];
+    }
+}
+
+// Breadth-first order of the first max_top internal nodes; children that are
+// themselves staged are re-pointed at the shared-memory table.
+__global__ void __launch_bounds__(kThreads) k_build_top(const float4* __restrict__ nodes, int n_internal, int max_top,
+                                                         int* __restrict__ top_index, float4* __restrict__ top_nodes,
+                                                         uint32_t* __restrict__ n_top_out) {
+    extern __shared__ int queue[];
+    __shared__ int s_count;
+    if (threadIdx.x == 0) {
+        int head = 0, tail = 0;
+        if (max_top > 0) {
+            queue[tail] = 0;
+            top_index[0] = 0;
+            tail = 1;
+        }
+        while (head < tail) {
+            const int g = queue[head++];
+            const float4 n3 = nodes[4 * g + 3];
+            const uint32_t c[2] = {__float_as_uint(n3.x), __float_as_uint(n3.y)};
+            for (int k = 0; k < 2; k++) {
+                if (!(c[k] & RTW_REF_LEAF) && tail < max_top && (int)c[k] < n_internal && top_index[c[k]] < 0) {
+                    top_index[c[k]] = tail;
+                    queue[tail++] = (int)c[k];
+                }
+            }
+        }
+        s_count = tail;
+        *n_top_out = (uint32_t)tail;
+        __threadfence_block();
+    }
+    __syncthreads();
+    const int count = s_count;
+    for (int j = threadIdx.x; j < count; j += blockDim.x) {
+        const int g = queue[j];
+        float4 n3 = nodes[4 * g + 3];
+        uint32_t cl = __float_as_uint(n3.x), cr = __float_as_uint(n3.y);
+        if (!(cl & RTW_REF_LEAF) && top_index[cl] >= 0) cl = RTW_REF_TOP | (uint32_t)top_index[cl];
+        if (!(cr & RTW_REF_LEAF) && top_index[cr] >= 0) cr = RTW_REF_TOP | (uint32_t)top_index[cr];
+        n3.x = __uint_as_float(cl);
+        n3.y = __uint_as_float(cr);
+        top_nodes[4 * j + 0] = nodes[4 * g + 0];
+        top_nodes[4 * j + 1] = nodes[4 * g + 1];
+        top_nodes[4 * j + 2] = nodes[4 * g + 2];
+        top_nodes[4 * j + 3] = n3;
+    }
+}
+
+}  // namespace
+
+cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches) {
+    const int n = b.n;
+    const int nb = (n + kThreads - 1) / kThreads;
+    uint64_t l = 0;
+    k_bounds_init<<<1, 32, 0, s>>>(b.bounds);
+    k_prim_aabb<<<nb, kThreads, 0, s>>>(b.prims, b.xforms, n, b.box_mn, b.box_mx, b.bounds);
+    k_morton<<<nb, kThreads, 0, s>>>(b.box_mn, b.box_mx, n, b.bounds, b.keys[0], b.vals[0]);
+    l += 3;
+    unsigned long long* keys[2] = {b.keys[0], b.keys[1]};
+    uint32_t* vals[2] = {b.vals[0], b.vals[1]};
+    cudaError_t e = sort_pairs(s, keys, vals, n, b.hist, &l);
+    if (e != cudaSuccess) return e;
+    k_pack_leaves<<<nb, kThreads, 0, s>>>(b.prims, b.mats_raw, n, b.vals[0], b.box_mn, b.box_mx, b.leaf_mn, b.leaf_mx,
+                                          b.prims_packed, b.prim_ext, b.leaf_prim, b.leaf_mat);
+    l += 1;
+    int n_internal;
+    if (n == 1) {
+        n_internal = 1;
+        k_single_leaf<<<1, 1, 0, s>>>(b.leaf_mn, b.leaf_mx, b.nodes, b.parent, b.top_index);
+        l += 1;
+    } else {
+        n_internal = n - 1;
+        const int nbi = (n_internal + kThreads - 1) / kThreads;
+        k_karras<<<nbi, kThreads, 0, s>>>(b.keys[0], n, b.nodes, b.parent, b.leaf_parent, b.flags, b.top_index);
+        k_refit<<<nb, kThreads, 0, s>>>(n, b.leaf_parent, b.parent, b.flags, b.leaf_mn, b.leaf_mx, b.nodes);
+        l += 2;
+    }
+    const int max_top = b.max_top < n_internal ? b.max_top : n_internal;
+    k_build_top<<<1, kThreads, sizeof(int) * (max_top > 0 ? max_top : 1), s>>>(b.nodes, n_internal, max_top, b.top_index,
+                                                                              b.top_nodes, b.bounds + 6);
+    l += 1;
+    if (launches) *launches += l;
+    return cudaGetLastError();
+}
+
+}  // namespace rtw
