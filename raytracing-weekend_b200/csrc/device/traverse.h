@@ -33,14 +33,17 @@ RTW_HD void fetch_node(const DScene& sc, const float4* top, uint32_t ref, float4
 }
 
 // Conservative slab test of both children against [tmin, limit].
-// t = fma(bound, 1/d, -o/d); NaNs (0 * inf) drop out of fminf/fmaxf, which only
-// widens the interval.  The far side is padded by 2 ulp-ish (Ize 2013).
+// t = fma(bound, 1/d, -o/d); any NaN drops out of fminf/fmaxf, which only widens
+// the interval.  The far side is padded by 2 ulp-ish (Ize 2013).
 struct SlabRay {
     float3 inv, ood;
 };
+// |d| < 1e-30 is replaced by +-1e-30: with a true 1/0 the fma form gives inf - inf.
+// The slab then spans (-huge, +huge) when the origin is inside it, as it should.
+RTW_HD float safe_inv(float d) { return 1.0f / (fabsf(d) < 1e-30f ? copysignf(1e-30f, d) : d); }
 RTW_HD SlabRay make_slab_ray(const RayW& r) {
     SlabRay s;
-    s.inv = f3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    s.inv = f3(safe_inv(r.d.x), safe_inv(r.d.y), safe_inv(r.d.z));
     s.ood = f3(r.o.x * s.inv.x, r.o.y * s.inv.y, r.o.z * s.inv.z);
     return s;
 }

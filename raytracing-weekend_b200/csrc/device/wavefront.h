@@ -72,7 +72,8 @@ RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsig
     w.ray_d[slot] = make_float4(direction.x, direction.y, direction.z, gather);
     w.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
     w.rad[slot] = make_float4(0.f, 0.f, 0.f, u2f(pixel));
-    w.misc[slot] = make_uint2(misc_pack(0, RTW_ST_ALIVE), lseed);
+    // `while (depth < maxRayDepth)` (raygen.cu:36): with a depth limit of 0 no ray is traced
+    w.misc[slot] = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
 }
 
 // ---- stage 1: closest-hit traversal + material classification --------------
