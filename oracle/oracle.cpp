@@ -164,12 +164,15 @@ struct Ray {
 };
 
 struct Counters {
-    uint64_t paths = 0, rays_closest = 0, rays_shadow = 0, nodes = 0, prims = 0, vertices = 0;
+    uint64_t paths = 0, rays_closest = 0, rays_shadow = 0, vertices = 0;
+    uint64_t nodes_c = 0, prims_c = 0, xf_c = 0, nodes_s = 0, prims_s = 0, xf_s = 0;
     void add_to(orc_counters* o) const {
         if (!o) return;
         o->paths += paths; o->rays_closest += rays_closest; o->rays_shadow += rays_shadow;
-        o->nodes_visited += nodes; o->prims_tested += prims; o->vertices_shaded += vertices;
+        o->nodes_visited += nodes_c + nodes_s; o->prims_tested += prims_c + prims_s; o->vertices_shaded += vertices;
         o->shadow_enqueued += rays_shadow;
+        o->nodes_closest += nodes_c; o->prims_closest += prims_c; o->prims_xf_closest += xf_c;
+        o->nodes_shadow += nodes_s; o->prims_shadow += prims_s; o->prims_xf_shadow += xf_s;
     }
 };
 
@@ -637,6 +640,13 @@ static inline bool slab(V3 mn, V3 mx, V3 o, V3 inv, float tmin, float tlimit, fl
 // ============================================================================
 // Traversal: closest hit / any hit
 // ============================================================================
+static inline bool has_xf(const orc_scene& s, int pi) {
+    return s.prims[pi].type != RTW_PRIM_MOVING_SPHERE && s.prims[pi].transform >= 0;
+}
+
+// Same traversal order as the device kernel (near child first, far child pushed,
+// children culled against the current best t) so that the visit counters describe
+// the work the CUDA traversal does on the same LBVH.
 static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_best, int& prim_best, Counters& c) {
     c.rays_closest++;
     t_best = 0.f;
@@ -644,7 +654,8 @@ static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_b
     bool found = false;
     auto consider = [&](int pi) {
         float t;
-        c.prims++;
+        c.prims_c++;
+        if (has_xf(s, pi)) c.xf_c++;
         if (candidate(s, pi, r, t)) {
             if (!found || t < t_best || (t == t_best && pi < prim_best)) {
                 found = true;
@@ -660,63 +671,72 @@ static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_b
     V3 inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
     int stack[128];
     int sp = 0;
-    stack[sp++] = 0;
-    while (sp > 0) {
-        int ni = stack[--sp];
-        const BvhNode& nd = s.nodes[ni];
-        c.nodes++;
-        float limit = found ? t_best : r.tmax;
-        float tl, tr;
-        bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, limit, tl);
-        bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, limit, tr);
-        // volumes report hits beyond their exit point, but never before the box entry;
-        // NaN-direction rays (0 * inf) fall through to a conservative visit.
-        if (tl != tl) hl = true;
-        if (tr != tr) hr = true;
-        int refs[2] = {nd.left, nd.right};
-        bool hits[2] = {hl, hr};
-        for (int k = 0; k < 2; k++) {
-            if (!hits[k]) continue;
-            if (refs[k] < 0) consider(s.leaf_prim[~refs[k]]);
-            else if (sp < 128) stack[sp++] = refs[k];
+    int cur = 0;  // >= 0 internal node, < 0 leaf ~ref
+    for (;;) {
+        if (cur < 0) {
+            consider(s.leaf_prim[~cur]);
+        } else {
+            const BvhNode& nd = s.nodes[cur];
+            c.nodes_c++;
+            float limit = found ? t_best : r.tmax;
+            float tl, tr;
+            bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, limit, tl);
+            bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, limit, tr);
+            if (tl != tl) hl = true;   // all-NaN slab: visit
+            if (tr != tr) hr = true;
+            if (hl && hr) {
+                bool left_first = !(tr < tl);
+                if (sp < 128) stack[sp++] = left_first ? nd.right : nd.left;
+                cur = left_first ? nd.left : nd.right;
+                continue;
+            }
+            if (hl) { cur = nd.left; continue; }
+            if (hr) { cur = nd.right; continue; }
         }
+        if (sp == 0) break;
+        cur = stack[--sp];
     }
     return found;
 }
 
 static bool trace_any(const orc_scene& s, const Ray& r, int mode, Counters& c) {
     c.rays_shadow++;
+    auto test = [&](int pi) {
+        float t;
+        c.prims_s++;
+        if (has_xf(s, pi)) c.xf_s++;
+        return candidate(s, pi, r, t);
+    };
     if (mode == 0 || !s.bvh_built) {
-        for (int i = 0; i < (int)s.prims.size(); i++) {
-            float t;
-            c.prims++;
-            if (candidate(s, i, r, t)) return true;
-        }
+        for (int i = 0; i < (int)s.prims.size(); i++)
+            if (test(i)) return true;
         return false;
     }
     V3 inv = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
     int stack[128];
     int sp = 0;
-    stack[sp++] = 0;
-    while (sp > 0) {
-        int ni = stack[--sp];
-        const BvhNode& nd = s.nodes[ni];
-        c.nodes++;
-        float tl, tr;
-        bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, r.tmax, tl);
-        bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, r.tmax, tr);
-        if (tl != tl) hl = true;
-        if (tr != tr) hr = true;
-        int refs[2] = {nd.left, nd.right};
-        bool hits[2] = {hl, hr};
-        for (int k = 0; k < 2; k++) {
-            if (!hits[k]) continue;
-            if (refs[k] < 0) {
-                float t;
-                c.prims++;
-                if (candidate(s, s.leaf_prim[~refs[k]], r, t)) return true;
-            } else if (sp < 128) stack[sp++] = refs[k];
+    int cur = 0;
+    for (;;) {
+        if (cur < 0) {
+            if (test(s.leaf_prim[~cur])) return true;
+        } else {
+            const BvhNode& nd = s.nodes[cur];
+            c.nodes_s++;
+            float tl, tr;
+            bool hl = slab(nd.lmin, nd.lmax, r.o, inv, r.tmin, r.tmax, tl);
+            bool hr = slab(nd.rmin, nd.rmax, r.o, inv, r.tmin, r.tmax, tr);
+            if (tl != tl) hl = true;
+            if (tr != tr) hr = true;
+            if (hl && hr) {
+                if (sp < 128) stack[sp++] = nd.right;
+                cur = nd.left;
+                continue;
+            }
+            if (hl) { cur = nd.left; continue; }
+            if (hr) { cur = nd.right; continue; }
         }
+        if (sp == 0) break;
+        cur = stack[--sp];
     }
     return false;
 }

@@ -34,6 +34,11 @@ typedef struct orc_counters {
     uint64_t prims_tested;
     uint64_t vertices_shaded;    /* closest-hit shader invocations */
     uint64_t shadow_enqueued;    /* == rays_shadow */
+    /* split of nodes_visited / prims_tested (BVH mode), feeding the algorithmic
+       bytes/ray of SURVEY.md §8d: closest-hit rays vs shadow rays, and how many of
+       the tested primitives carry an instance transform (80 B instead of 32 B) */
+    uint64_t nodes_closest, prims_closest, prims_xf_closest;
+    uint64_t nodes_shadow, prims_shadow, prims_xf_shadow;
 } orc_counters;
 
 /* ---- RNG (lib/random.cuh:7-38; SDK cuda/random.h lcg/rnd) ---- */

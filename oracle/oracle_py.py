@@ -16,7 +16,9 @@ LIB_PATH = os.path.join(_HERE, "liboracle.so")
 class Counters(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64), ("vertices_shaded", C.c_uint64),
-                ("shadow_enqueued", C.c_uint64)]
+                ("shadow_enqueued", C.c_uint64),
+                ("nodes_closest", C.c_uint64), ("prims_closest", C.c_uint64), ("prims_xf_closest", C.c_uint64),
+                ("nodes_shadow", C.c_uint64), ("prims_shadow", C.c_uint64), ("prims_xf_shadow", C.c_uint64)]
 
     def as_dict(self):
         return {k: int(getattr(self, k)) for k, _ in self._fields_}

@@ -55,7 +55,6 @@ extern "C" int rtw_create(int device, rtw_ctx** out) {
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_end);
     for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ring_events[i], cudaEventDisableTiming);
-    for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreate(&c->stage_events[i]);
     if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&c->h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8);
     if (e != cudaSuccess) {
         g_create_error = std::string("context setup: ") + cudaGetErrorString(e);
@@ -83,7 +82,7 @@ extern "C" int rtw_destroy(rtw_ctx* c) {
     free_frame(c);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     for (auto& e : c->ring_events) if (e) cudaEventDestroy(e);
-    for (auto& e : c->stage_events) if (e) cudaEventDestroy(e);
+    for (auto& e : c->prof_events) if (e) cudaEventDestroy(e);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
     if (c->stream) cudaStreamDestroy(c->stream);

@@ -31,7 +31,7 @@ struct rtw_ctx {
     uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
     cudaEvent_t ring_events[8] = {};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    cudaEvent_t stage_events[5] = {};
+    std::vector<cudaEvent_t> prof_events;  // 5 per sampled iteration (profile option)
 
     // ---- last frame ----
     float4* d_accum = nullptr;          // linear sums of the last rtw_render

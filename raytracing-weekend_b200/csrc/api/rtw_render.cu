@@ -73,21 +73,27 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     const int lag = c->opt_lag;
     uint64_t iter = 0;
     bool done = (total == 0);
+    // Per-stage timing (option "profile"): CUDA events around the stages of SAMPLED
+    // iterations, read back after the frame — no host sync inside the frame.
+    const int kMaxSampled = 256;
+    uint64_t prof_stride = 1;
+    int sampled = 0;
+    if (c->opt_profile) {
+        const uint64_t est = total / (uint64_t)P * 5 + 24;   // ~5 bounces per path
+        prof_stride = est / kMaxSampled + 1;
+        while ((int)c->prof_events.size() < 5 * kMaxSampled) {
+            cudaEvent_t e = nullptr;
+            RTW_CUDA(c, cudaEventCreate(&e));
+            c->prof_events.push_back(e);
+        }
+    }
     while (!done) {
-        cudaEvent_t* sev = c->opt_profile ? c->stage_events : nullptr;
+        cudaEvent_t* sev = nullptr;
+        if (c->opt_profile && sampled < kMaxSampled && iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
         RTW_CUDA(c, wavefront_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
         uint32_t* snap = c->h_counters + (iter % 8) * RTW_C_WORDS;
         RTW_CUDA(c, cudaMemcpyAsync(snap, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, c->stream));
         RTW_CUDA(c, cudaEventRecord(c->ring_events[iter % 8], c->stream));
-        if (sev) {
-            RTW_CUDA(c, cudaEventSynchronize(sev[4]));
-            float a = 0, b = 0, d = 0, e = 0;
-            cudaEventElapsedTime(&a, sev[0], sev[1]);
-            cudaEventElapsedTime(&b, sev[1], sev[2]);
-            cudaEventElapsedTime(&d, sev[2], sev[3]);
-            cudaEventElapsedTime(&e, sev[3], sev[4]);
-            st.logic_ms += a; st.traverse_ms += b; st.shade_ms += d; st.shadow_ms += e;
-        }
         iter++;
         if (iter >= (uint64_t)lag) {
             const uint64_t j = iter - lag;
@@ -109,6 +115,19 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     st.rays_shadow = u64_at(fin, RTW_C_SHRAYS_LO);
     st.kernel_launches = launches;
     st.iterations = iter;
+    if (sampled > 0) {
+        double a = 0, b = 0, d = 0, e = 0;
+        for (int i = 0; i < sampled; i++) {
+            cudaEvent_t* ev = c->prof_events.data() + 5 * i;
+            float x = 0;
+            cudaEventElapsedTime(&x, ev[0], ev[1]); a += x;
+            cudaEventElapsedTime(&x, ev[1], ev[2]); b += x;
+            cudaEventElapsedTime(&x, ev[2], ev[3]); d += x;
+            cudaEventElapsedTime(&x, ev[3], ev[4]); e += x;
+        }
+        const double scale = (double)iter / (double)sampled;   // extrapolate to all iterations
+        st.logic_ms = a * scale; st.traverse_ms = b * scale; st.shade_ms = d * scale; st.shadow_ms = e * scale;
+    }
     return RTW_OK;
 }
 

@@ -1,0 +1,49 @@
+// director.cpp — see director.h.  Errors: the reference throws sutil::Exception that
+// nothing catches (→ std::terminate) and exits on an unknown scene (Director.cpp:955-958);
+// here every C-ABI status is checked and reported before exit(EXIT_FAILURE).
+#include "director.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+
+void Director::check(int rc, const char* what) {
+    if (rc == RTW_OK) return;
+    std::cerr << "ERROR: " << what << " failed (" << rc << "): " << rtw_last_error(m_ctx) << std::endl;
+    std::exit(EXIT_FAILURE);
+}
+
+void Director::init(unsigned int width, unsigned int height, unsigned int samples) {
+    m_Nx = (int)width;
+    m_Ny = (int)height;
+    m_Ns = (int)samples;
+    check(rtw_create(m_device, &m_ctx), "rtw_create");
+    if (_debug) check(rtw_set_option(m_ctx, "profile", 1), "rtw_set_option(profile)");
+}
+
+void Director::createScene(unsigned int sceneNumber) {
+    int rc = rtw_scene_create((int)sceneNumber, m_Nx, m_Ny, m_assets.c_str(), 0, &m_scene);
+    if (rc != RTW_OK) std::exit(EXIT_FAILURE);  // "ERROR: Scene N unknown." already printed
+    check(rtw_upload_scene(m_ctx, rtw_scene_get_desc(m_scene)), "rtw_upload_scene");
+    check(rtw_build_accel(m_ctx), "rtw_build_accel");
+    if (_verbose) std::cerr << "INFO: Scene description: " << rtw_scene_description(m_scene) << std::endl;  // Director.cpp:965-968
+}
+
+void Director::renderFrame() {
+    m_frame.assign((size_t)m_Nx * m_Ny * 4, 0.f);
+    check(rtw_render(m_ctx, m_Nx, m_Ny, m_Ns, m_maxRayDepth, m_frame.data()), "rtw_render");
+    check(rtw_get_stats(m_ctx, &m_stats), "rtw_get_stats");
+}
+
+void Director::printPPM(const char* path) {
+    int rc = rtw_write_ppm(path, m_Nx, m_Ny, m_frame.data());
+    if (rc != RTW_OK) {
+        std::cerr << "ERROR: cannot write " << path << std::endl;
+        std::exit(EXIT_FAILURE);
+    }
+}
+
+void Director::destroy() {
+    if (m_scene) { rtw_scene_free(m_scene); m_scene = nullptr; }
+    if (m_ctx) { rtw_destroy(m_ctx); m_ctx = nullptr; }
+}
