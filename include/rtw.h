@@ -271,6 +271,14 @@ int  rtw_trace_any(rtw_ctx* ctx, const rtw_ray* rays, int n, int32_t* occluded);
 int  rtw_rng_stream(rtw_ctx* ctx, uint32_t seed0, uint32_t seed1, int n,
                     uint32_t* tea_out, uint32_t* lcg_out, float* rnd_out,
                     uint32_t* xs_out, float* randf_out);
+/* The path's transcendental functions as the device computes them (the arithmetic
+ * contract of DESIGN.md; they replace CUDA libm's sinf/cosf/logf/powf(x,5)/atan2f/asinf
+ * at the call sites lib/sampling.cuh:16-19,55-56, geometry/volumeBox.cu:79,
+ * material/dielectricMaterial.cu:25, geometry/sphere.cu:27-28).  out[i] = fn(x[i], y[i]);
+ * y is only read by RTW_FN_ATAN2 (out = atan2(x = ordinate, y = abscissa)) and may be NULL otherwise. */
+enum rtw_math_fn { RTW_FN_SIN = 0, RTW_FN_COS = 1, RTW_FN_LOG = 2, RTW_FN_POW5 = 3, RTW_FN_ATAN2 = 4, RTW_FN_ASIN = 5,
+                   RTW_FN_COUNT = 6 };
+int  rtw_math_eval(rtw_ctx* ctx, int fn, const float* x, const float* y, int n, float* out);
 /* Sample-0 camera rays as the device generates them (raygen/raygen.cu:129-135,
  * shaders/camera.cu:11-19); rays_out has Nx*Ny entries. */
 int  rtw_camera_rays(rtw_ctx* ctx, int Nx, int Ny, int sample, rtw_ray* rays_out);

@@ -6,6 +6,7 @@
 // exactly as the expression is written.
 #include "oracle.h"
 #include "vecmath.h"
+#include "detmath.h"
 
 #include <algorithm>
 #include <atomic>
@@ -52,6 +53,19 @@ static inline uint32_t lcg(uint32_t& prev) {
     return prev & 0x00FFFFFF;
 }
 static inline float rnd(uint32_t& prev) { return ((float)lcg(prev) / (float)0x01000000); }
+
+extern "C" void orc_math_eval(int fn, const float* x, const float* y, int n, float* out) {
+    for (int i = 0; i < n; i++) {
+        switch (fn) {
+            case RTW_FN_SIN: out[i] = dm::sin(x[i]); break;
+            case RTW_FN_COS: out[i] = dm::cos(x[i]); break;
+            case RTW_FN_LOG: out[i] = dm::log(x[i]); break;
+            case RTW_FN_POW5: out[i] = dm::pow5(x[i]); break;
+            case RTW_FN_ATAN2: out[i] = dm::atan2(x[i], y[i]); break;
+            default: out[i] = dm::asin(x[i]); break;
+        }
+    }
+}
 
 extern "C" uint32_t orc_tea(uint32_t rounds, uint32_t s0, uint32_t s1) { return tea_n(rounds, s0, s1); }
 
@@ -186,8 +200,8 @@ struct Counters {
 
 // geometry/sphere.cu:24-32
 static inline void get_sphere_uv(V3 p, float& u, float& v) {
-    float phi = atan2f(p.z, p.x);
-    float theta = asinf(p.y);
+    float phi = dm::atan2(p.z, p.x);
+    float theta = dm::asin(p.y);
     u = 1 - (phi + kPi) / (2.f * kPi);
     v = (theta + kPiO2) / kPi;
 }
@@ -324,7 +338,7 @@ static bool candidate(const orc_scene& s, int pi, const Ray& r, float& t_out) {
         if (hitt1 < 0.f) hitt1 = 0.f;
         // distanceInsideBoundary computed but never compared (Q23)
         uint32_t st = medium_state(r.seed, pi);
-        float hitDistance = -(1.f / density) * logf(randf(st));
+        float hitDistance = -(1.f / density) * dm::log(randf(st));
         float hitt = hitt1 + (hitDistance / length(d));
         if (!(hitt >= tmin && hitt <= tmax)) return false;
         t_out = hitt;
@@ -342,7 +356,7 @@ static bool candidate(const orc_scene& s, int pi, const Ray& r, float& t_out) {
         if (hitt1 >= hitt2) return false;
         if (hitt1 < 0.f) hitt1 = 0.f;
         uint32_t st = medium_state(r.seed, pi);
-        float hitDistance = -(1.f / density) * logf(rnd(st));
+        float hitDistance = -(1.f / density) * dm::log(rnd(st));
         float hitt = hitt1 + (hitDistance / length(d));
         if (!(hitt >= tmin && hitt <= tmax)) return false;
         t_out = hitt;
@@ -773,7 +787,7 @@ extern "C" void orc_trace_any(const orc_scene* s, const rtw_ray* rays, int n, in
 // lib/sampling.cuh:15-22
 static inline V3 random_in_unit_disk(uint32_t& seed) {
     float a = rnd(seed) * 2.0f * kPi;
-    V3 xy = v3(sinf(a), cosf(a), 0);
+    V3 xy = v3(dm::sin(a), dm::cos(a), 0);
     xy *= sqrtf(rnd(seed));
     return xy;
 }
@@ -793,8 +807,8 @@ static inline V3 randomCosineDirection(uint32_t& seed) {
     float r1 = rnd(seed);
     float r2 = rnd(seed);
     float phi = 2.f * kPi * r1;
-    float x = cosf(phi) * 2 * sqrtf(r2);
-    float y = sinf(phi) * 2 * sqrtf(r2);
+    float x = dm::cos(phi) * 2 * sqrtf(r2);
+    float y = dm::sin(phi) * 2 * sqrtf(r2);
     float z = sqrtf(1 - r2);
     return v3(x, y, z);
 }
@@ -892,7 +906,7 @@ static V3 texture_eval(const orc_scene& s, int ti, float u, float v, V3 p, int d
     case RTW_TEX_CONSTANT:  // texture/constantTexture.cu:5-10
         return v3(t.color);
     case RTW_TEX_CHECKER: {  // texture/checkeredTexture.cu:9-20 (Q18: children dispatched correctly)
-        float sines = sinf(10.f * p.x) * sinf(10.f - p.y) * sinf(10.f * p.z);
+        float sines = dm::sin(10.f * p.x) * dm::sin(10.f - p.y) * dm::sin(10.f * p.z);
         if (sines < 0) return texture_eval(s, t.odd, u, v, p, depth + 1);
         return texture_eval(s, t.even, u, v, p, depth + 1);
     }
@@ -900,7 +914,7 @@ static V3 texture_eval(const orc_scene& s, int ti, float u, float v, V3 p, int d
         return image_lookup(s.images[t.image], u, v);
     case RTW_TEX_NOISE: {  // texture/noiseTexture.cu:72-83
         const rtw_perlin& tab = s.perlin[t.perlin];
-        return v3(1.f) * 0.5f * (1.0f + sinf(t.scale * p.z + 5.f * perlin_turb(tab, t.scale * p)));
+        return v3(1.f) * 0.5f * (1.0f + dm::sin(t.scale * p.z + 5.f * perlin_turb(tab, t.scale * p)));
     }
     default:  // texture/nullTexture.cu:7-12
         return v3(0.f, 0.f, 0.f);
@@ -966,7 +980,7 @@ static void mat_metal(const orc_scene& s, const rtw_material& m, PerRayData& prd
 static inline float fresnelSchlick(float cosThetaI, float etaI, float etaT) {
     float r0 = (etaI - etaT) / (etaI + etaT);
     r0 = r0 * r0;
-    return r0 + (1.f - r0) * powf((1.f - cosThetaI), 5.f);
+    return r0 + (1.f - r0) * dm::pow5((1.f - cosThetaI));
 }
 // material/dielectricMaterial.cu:37-114
 static void mat_dielectric(const orc_scene&, const rtw_material& m, PerRayData& prd, V3 direction, const HitRecord& h) {

@@ -47,6 +47,9 @@ void orc_rng_stream(uint32_t seed0, uint32_t seed1, int n,
                     uint32_t* tea_out, uint32_t* lcg_out, float* rnd_out,
                     uint32_t* xs_out, float* randf_out);
 
+/* ---- arithmetic contract (oracle/detmath.h): fn numbered like rtw_math_fn ---- */
+void orc_math_eval(int fn, const float* x, const float* y, int n, float* out);
+
 /* ---- scene ---- */
 int  orc_scene_load(const rtw_scene_desc* desc, orc_scene** out);   /* deep copy */
 void orc_scene_free(orc_scene* s);

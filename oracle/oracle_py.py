@@ -39,6 +39,8 @@ def lib():
     L.orc_tea.argtypes = [u32, u32, u32]
     L.orc_rng_stream.restype = None
     L.orc_rng_stream.argtypes = [u32, u32, i32, vp, vp, vp, vp, vp]
+    L.orc_math_eval.restype = None
+    L.orc_math_eval.argtypes = [i32, vp, vp, i32, vp]
     L.orc_scene_load.restype = i32
     L.orc_scene_load.argtypes = [vp, C.POINTER(vp)]
     L.orc_scene_free.restype = None
@@ -73,6 +75,15 @@ def lib():
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def math_eval(fn, x, y=None):
+    """oracle/detmath.h: fn numbered like rtw_math_fn (0 sin, 1 cos, 2 log, 3 pow5, 4 atan2, 5 asin)."""
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(x)
+    yy = np.ascontiguousarray(y, np.float32) if y is not None else None
+    lib().orc_math_eval(fn, _ptr(x), _ptr(yy) if yy is not None else None, len(x), _ptr(out))
+    return out
 
 
 RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("tmin", "<f4"), ("dir", "<f4", 3), ("tmax", "<f4"), ("time", "<f4"),

@@ -115,7 +115,7 @@ ABI_SYMBOLS = [
     "rtw_build_accel", "rtw_render", "rtw_render_accum", "rtw_tonemap", "rtw_get_linear", "rtw_set_option",
     "rtw_get_stats", "rtw_trace_closest", "rtw_trace_any", "rtw_rng_stream", "rtw_camera_rays", "rtw_bvh_info_get",
     "rtw_bvh_download", "rtw_sort_pairs", "rtw_scene_create", "rtw_scene_get_desc", "rtw_scene_description",
-    "rtw_scene_free", "rtw_write_ppm",
+    "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval",
 ]
 
 _lib = None
@@ -154,6 +154,7 @@ def lib():
         "rtw_trace_any": (i32, [vp, vp, i32, vp]),
         "rtw_rng_stream": (i32, [vp, u32, u32, i32, vp, vp, vp, vp, vp]),
         "rtw_camera_rays": (i32, [vp, i32, i32, i32, vp]),
+        "rtw_math_eval": (i32, [vp, i32, vp, vp, i32, vp]),
         "rtw_bvh_info_get": (i32, [vp, C.POINTER(BvhInfo)]),
         "rtw_bvh_download": (i32, [vp, vp, vp, vp, vp, vp]),
         "rtw_sort_pairs": (i32, [vp, vp, vp, i32]),
@@ -297,6 +298,14 @@ class Director:
         self._check(lib().rtw_rng_stream(self._c, seed0, seed1, n, _ptr(tea), _ptr(lcg), _ptr(rnd), _ptr(xs), _ptr(rf)),
                     "rtw_rng_stream")
         return int(tea[0]), lcg, rnd, xs, rf
+
+    def math_eval(self, fn, x, y=None):
+        """Device evaluation of the arithmetic-contract functions (rtw_math_fn numbering)."""
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.empty_like(x)
+        yp = _ptr(np.ascontiguousarray(y, np.float32)) if y is not None else None
+        self._check(lib().rtw_math_eval(self._c, fn, _ptr(x), yp, len(x), _ptr(out)), "rtw_math_eval")
+        return out
 
     def camera_rays(self, sample=0):
         rays = np.empty(self.Nx * self.Ny, dtype=RAY_DTYPE)

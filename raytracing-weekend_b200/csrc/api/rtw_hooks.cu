@@ -68,6 +68,25 @@ extern "C" int rtw_rng_stream(rtw_ctx* c, uint32_t seed0, uint32_t seed1, int n,
     return RTW_OK;
 }
 
+extern "C" int rtw_math_eval(rtw_ctx* c, int fn, const float* x, const float* y, int n, float* out) {
+    if (!c || fn < 0 || fn >= RTW_FN_COUNT || !x || !out || n < 0 || (fn == RTW_FN_ATAN2 && !y)) return RTW_ERR_INVALID;
+    if (n == 0) return RTW_OK;
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    Tmp t;
+    float *d_x = nullptr, *d_y = nullptr, *d_o = nullptr;
+    RTW_CUDA(c, dalloc(t.pool, &d_x, n));
+    RTW_CUDA(c, dalloc(t.pool, &d_o, n));
+    RTW_CUDA(c, cudaMemcpyAsync(d_x, x, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+    if (fn == RTW_FN_ATAN2) {
+        RTW_CUDA(c, dalloc(t.pool, &d_y, n));
+        RTW_CUDA(c, cudaMemcpyAsync(d_y, y, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+    }
+    RTW_CUDA(c, launch_math_eval(c->stream, fn, d_x, d_y, n, d_o));
+    RTW_CUDA(c, cudaMemcpyAsync(out, d_o, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTW_OK;
+}
+
 extern "C" int rtw_camera_rays(rtw_ctx* c, int Nx, int Ny, int sample, rtw_ray* rays_out) {
     if (!c || Nx <= 0 || Ny <= 0 || sample < 0 || !rays_out) return RTW_ERR_INVALID;
     if (!c->scene_loaded) return fail(c, RTW_ERR_STATE, "camera rays before rtw_upload_scene");

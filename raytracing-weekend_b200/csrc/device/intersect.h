@@ -10,6 +10,7 @@
 // optixReportIntersection accepts iff tmin <= t <= tmax, and the closest hit is
 // the lexicographic minimum of (t, primitive index) — independent of traversal order.
 #pragma once
+#include "detmath.h"
 #include "layout.h"
 #include "rng.h"
 
@@ -177,7 +178,7 @@ RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, float
 #endif
     uint32_t st = medium_state(r.seed, (uint32_t)prim);
     float u = (type == RTW_PRIM_VOLUME_BOX) ? randf(st) : rnd(st);  // volumeBox.cu:79 / volumeSphere.cu:93
-    float hitDistance = -(1.f / density) * logf(u);
+    float hitDistance = -(1.f / density) * det_logf(u);
     float hitt = hitt1 + (hitDistance / length(d));
     if (!(hitt >= tmin && hitt <= tmax)) return false;
     t_out = hitt;
@@ -192,8 +193,8 @@ struct HitAttr {    // HitRecord, lib/raydata.cuh:117-124
 
 // geometry/sphere.cu:24-32
 RTW_HD void get_sphere_uv(float3 p, float& u, float& v) {
-    float phi = atan2f(p.z, p.x);
-    float theta = asinf(p.y);
+    float phi = det_atan2f(p.z, p.x);
+    float theta = det_asinf(p.y);
     u = 1 - (phi + RTW_PI) / (2.f * RTW_PI);
     v = (theta + RTW_PIO2) / RTW_PI;
 }

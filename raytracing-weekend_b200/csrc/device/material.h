@@ -5,6 +5,7 @@
 //   normalMaterial.cu:21-31
 //   pdf/rectPdf.cu:124-193 via pdf/mixturePdf.cu:25-38 (Q26)
 #pragma once
+#include "detmath.h"
 #include "intersect.h"
 #include "rng.h"
 #include "texture.h"
@@ -14,7 +15,9 @@ namespace rtw {
 // lib/sampling.cuh:15-22
 RTW_HD float3 random_in_unit_disk(uint32_t& seed) {
     float a = rnd(seed) * 2.0f * RTW_PI;
-    float3 xy = f3(sinf(a), cosf(a), 0);
+    float sa, ca;
+    det_sincosf(a, sa, ca);
+    float3 xy = f3(sa, ca, 0);
     xy = xy * sqrtf(rnd(seed));
     return xy;
 }
@@ -36,8 +39,10 @@ RTW_HD float3 randomCosineDirection(uint32_t& seed) {
     float r1 = rnd(seed);
     float r2 = rnd(seed);
     float phi = 2.f * RTW_PI * r1;
-    float x = cosf(phi) * 2 * sqrtf(r2);
-    float y = sinf(phi) * 2 * sqrtf(r2);
+    float sphi, cphi;
+    det_sincosf(phi, sphi, cphi);
+    float x = cphi * 2 * sqrtf(r2);
+    float y = sphi * 2 * sqrtf(r2);
     float z = sqrtf(1 - r2);
     return f3(x, y, z);
 }
@@ -104,7 +109,7 @@ RTW_HD void mat_metal(const DScene& sc, int tex, float fuzz, float3 direction, c
 RTW_HD float fresnelSchlick(float cosThetaI, float etaI, float etaT) {
     float r0 = (etaI - etaT) / (etaI + etaT);
     r0 = r0 * r0;
-    return r0 + (1.f - r0) * powf((1.f - cosThetaI), 5.f);
+    return r0 + (1.f - r0) * det_pow5f((1.f - cosThetaI));
 }
 
 // material/dielectricMaterial.cu:37-114 (Q13); lightDirection == -direction (raygen.cu:39)

@@ -2,6 +2,7 @@
 //   texture/constantTexture.cu:5-10, nullTexture.cu:7-12, checkeredTexture.cu:9-20,
 //   imageTexture.cu:10-16, noiseTexture.cu:19-83
 #pragma once
+#include "detmath.h"
 #include "layout.h"
 
 namespace rtw {
@@ -123,14 +124,14 @@ RTW_HDN inline float3 texture_eval(const DScene& sc, int tex, float u, float v, 
         const float4 t1 = ldg4(sc.texs + 2 * tex + 1);
         if (type == RTW_TEX_CHECKER) {
             // Q18: sine formula literal, children dispatched by texture index
-            float sines = sinf(10.f * p.x) * sinf(10.f - p.y) * sinf(10.f * p.z);
+            float sines = det_sinf(10.f * p.x) * det_sinf(10.f - p.y) * det_sinf(10.f * p.z);
             tex = (sines < 0) ? (int)f2u(t1.x) : (int)f2u(t1.y);
             continue;
         }
         if (type == RTW_TEX_IMAGE) return image_lookup(sc, (int)f2u(t1.w), u, v);
         if (type == RTW_TEX_NOISE) {
             const float scale = t1.z;
-            return f3(1.f) * 0.5f * (1.0f + sinf(scale * p.z + 5.f * perlin_turb(sc, (int)f2u(t1.w), scale * p)));
+            return f3(1.f) * 0.5f * (1.0f + det_sinf(scale * p.z + 5.f * perlin_turb(sc, (int)f2u(t1.w), scale * p)));
         }
         return f3(0.f, 0.f, 0.f);  // null texture
     }

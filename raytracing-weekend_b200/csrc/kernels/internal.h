@@ -66,6 +66,7 @@ cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg,
                          rtw_hit* hits, int32_t* occluded, uint64_t* launches);
 cudaError_t launch_rng_stream(cudaStream_t s, uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out,
                               uint32_t* lcg_out, float* rnd_out, uint32_t* xs_out, float* randf_out);
+cudaError_t launch_math_eval(cudaStream_t s, int fn, const float* x, const float* y, int n, float* out);
 cudaError_t launch_camera_rays(cudaStream_t s, const DScene& sc, const DWave& w, int sample, rtw_ray* rays_out);
 
 }  // namespace rtw

@@ -185,6 +185,23 @@ __global__ void k_rng_stream(uint32_t seed0, uint32_t seed1, int n, uint32_t* te
     }
 }
 
+__global__ void __launch_bounds__(kBlock) k_math_eval(int fn, const float* __restrict__ x, const float* __restrict__ y, int n,
+                                                       float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float a = x[i];
+    float r;
+    switch (fn) {
+        case RTW_FN_SIN: r = det_sinf(a); break;
+        case RTW_FN_COS: r = det_cosf(a); break;
+        case RTW_FN_LOG: r = det_logf(a); break;
+        case RTW_FN_POW5: r = det_pow5f(a); break;
+        case RTW_FN_ATAN2: r = det_atan2f(a, y[i]); break;
+        default: r = det_asinf(a); break;
+    }
+    out[i] = r;
+}
+
 __global__ void __launch_bounds__(kBlock) k_camera_rays(const DScene sc, const DWave w, rtw_ray* __restrict__ out) {
     const uint32_t npix = (uint32_t)w.Nx * (uint32_t)w.Ny;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -283,6 +300,12 @@ cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg,
 cudaError_t launch_rng_stream(cudaStream_t s, uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out,
                               uint32_t* lcg_out, float* rnd_out, uint32_t* xs_out, float* randf_out) {
     k_rng_stream<<<1, 32, 0, s>>>(seed0, seed1, n, tea_out, lcg_out, rnd_out, xs_out, randf_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_math_eval(cudaStream_t s, int fn, const float* x, const float* y, int n, float* out) {
+    if (n <= 0) return cudaSuccess;
+    k_math_eval<<<(n + kBlock - 1) / kBlock, kBlock, 0, s>>>(fn, x, y, n, out);
     return cudaGetLastError();
 }
 

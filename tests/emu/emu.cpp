@@ -366,3 +366,16 @@ extern "C" void emu_rng_stream(uint32_t seed0, uint32_t seed1, int n, uint32_t* 
         lcg_out[i] = lcg(a); rnd_out[i] = rnd(b); xs_out[i] = xorshift32(c); randf_out[i] = randf(d);
     }
 }
+
+extern "C" void emu_math_eval(int fn, const float* x, const float* y, int n, float* out) {
+    for (int i = 0; i < n; i++) {
+        switch (fn) {
+            case RTW_FN_SIN: out[i] = det_sinf(x[i]); break;
+            case RTW_FN_COS: out[i] = det_cosf(x[i]); break;
+            case RTW_FN_LOG: out[i] = det_logf(x[i]); break;
+            case RTW_FN_POW5: out[i] = det_pow5f(x[i]); break;
+            case RTW_FN_ATAN2: out[i] = det_atan2f(x[i], y[i]); break;
+            default: out[i] = det_asinf(x[i]); break;
+        }
+    }
+}

@@ -46,6 +46,7 @@ def lib():
     L.emu_render.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, vp, vp]
     L.emu_camera_rays.argtypes = [vp, i32, i32, i32, vp]
     L.emu_texture_eval.argtypes = [vp, i32, C.c_float, C.c_float, vp, vp]
+    L.emu_math_eval.argtypes = [i32, vp, vp, i32, vp]
     L.emu_rng_stream.argtypes = [C.c_uint32, C.c_uint32, i32, vp, vp, vp, vp, vp]
     _lib = L
     return L
@@ -122,3 +123,12 @@ def rng_stream(seed0, seed1, n):
     rf = np.zeros(n, np.float32)
     lib().emu_rng_stream(seed0, seed1, n, _ptr(t), _ptr(lcg), _ptr(rnd), _ptr(xs), _ptr(rf))
     return int(t[0]), lcg, rnd, xs, rf
+
+
+def math_eval(fn, x, y=None):
+    """csrc/device/detmath.h compiled for the host (fn numbered like rtw_math_fn)."""
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(x)
+    yy = np.ascontiguousarray(y, np.float32) if y is not None else None
+    lib().emu_math_eval(fn, _ptr(x), _ptr(yy) if yy is not None else None, len(x), _ptr(out))
+    return out
