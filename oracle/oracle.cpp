@@ -91,6 +91,8 @@ struct BvhNode {          // host mirror of the device LBVH node
     V3 lmin, lmax, rmin, rmax;
     int32_t left, right;  // >= 0 internal index, < 0 → leaf ~ref
     int32_t parent;
+    int32_t first, count; // the node spans leaves [first, first + count)
+    int32_t split;        // left child spans [first, split], right child [split + 1, first + count)
 };
 
 struct orc_scene {
@@ -108,6 +110,7 @@ struct orc_scene {
     int sky_light = 0;
     // host-mirror LBVH
     bool bvh_built = false;
+    int leaf_size = 1;    // subtrees of <= leaf_size leaves are walked as one primitive list (DESIGN.md "LBVH")
     std::vector<uint64_t> morton;
     std::vector<int32_t> leaf_prim;
     std::vector<BvhNode> nodes;
@@ -559,6 +562,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
     if (n == 1) {
         BvhNode& nd = s->nodes[0];
         nd.left = ~0; nd.right = ~0; nd.parent = -1;
+        nd.first = 0; nd.count = 1; nd.split = 0;
         nd.lmin = boxes[s->leaf_prim[0]].mn; nd.lmax = boxes[s->leaf_prim[0]].mx;
         nd.rmin = v3(FLT_MAX); nd.rmax = v3(FLT_MAX);  // unreachable point box
         s->bvh_built = true;
@@ -584,6 +588,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
         int gamma = i + sp * d + std::min(d, 0);
         int lo = std::min(i, j), hi = std::max(i, j);
         BvhNode& nd = s->nodes[i];
+        nd.first = lo; nd.count = hi - lo + 1; nd.split = gamma;
         if (lo == gamma) { nd.left = ~gamma; leaf_parent[gamma] = i; }
         else { nd.left = gamma; s->nodes[gamma].parent = i; }
         if (hi == gamma + 1) { nd.right = ~(gamma + 1); leaf_parent[gamma + 1] = i; }
@@ -608,6 +613,11 @@ extern "C" int orc_bvh_build(orc_scene* s) {
     }
     s->bvh_built = true;
     return 0;
+}
+
+extern "C" void orc_bvh_set_leaf_size(orc_scene* s, int leaf_size) {
+    if (leaf_size <= 0) leaf_size = (int)s->prims.size() <= 16 ? 16 : 4;   // the product's default (rtw_build_accel)
+    s->leaf_size = leaf_size > 32 ? 32 : leaf_size;
 }
 
 extern "C" int orc_bvh_info(const orc_scene* s, rtw_bvh_info* info) {
@@ -686,9 +696,15 @@ static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_b
     int stack[128];
     int sp = 0;
     int cur = 0;  // >= 0 internal node, < 0 leaf ~ref
+    const int n_leaves = (int)s.leaf_prim.size();
+    // a subtree of <= leaf_size leaves is not descended: its leaves are tested in order
+    auto is_range = [&](int ref) { return ref >= 0 && (n_leaves == 1 || s.nodes[ref].count <= s.leaf_size); };
     for (;;) {
         if (cur < 0) {
             consider(s.leaf_prim[~cur]);
+        } else if (is_range(cur)) {
+            const BvhNode& nd = s.nodes[cur];
+            for (int j = nd.first; j < nd.first + nd.count; j++) consider(s.leaf_prim[j]);
         } else {
             const BvhNode& nd = s.nodes[cur];
             c.nodes_c++;
@@ -730,9 +746,15 @@ static bool trace_any(const orc_scene& s, const Ray& r, int mode, Counters& c) {
     int stack[128];
     int sp = 0;
     int cur = 0;
+    const int n_leaves = (int)s.leaf_prim.size();
+    auto is_range = [&](int ref) { return ref >= 0 && (n_leaves == 1 || s.nodes[ref].count <= s.leaf_size); };
     for (;;) {
         if (cur < 0) {
             if (test(s.leaf_prim[~cur])) return true;
+        } else if (is_range(cur)) {
+            const BvhNode& nd = s.nodes[cur];
+            for (int j = nd.first; j < nd.first + nd.count; j++)
+                if (test(s.leaf_prim[j])) return true;
         } else {
             const BvhNode& nd = s.nodes[cur];
             c.nodes_s++;

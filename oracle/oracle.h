@@ -80,6 +80,9 @@ void orc_sample_radiance(const orc_scene* s, int Nx, int Ny, int x, int y, int k
 
 /* ---- host-mirror LBVH (same algorithm as the device builder) ---- */
 int  orc_bvh_build(orc_scene* s);
+/* subtrees of <= leaf_size leaves are tested as one primitive list (0 = the product's
+   default: 16 for scenes of <= 16 primitives, else 4); affects the visit counters only */
+void orc_bvh_set_leaf_size(orc_scene* s, int leaf_size);
 int  orc_bvh_info(const orc_scene* s, rtw_bvh_info* info);
 int  orc_bvh_download(const orc_scene* s, uint64_t* morton, int32_t* leaf_prim,
                       int32_t* left, int32_t* right, float* bounds);

@@ -61,6 +61,8 @@ def lib():
     L.orc_sample_radiance.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, vp]
     L.orc_bvh_build.restype = i32
     L.orc_bvh_build.argtypes = [vp]
+    L.orc_bvh_set_leaf_size.restype = None
+    L.orc_bvh_set_leaf_size.argtypes = [vp, i32]
     L.orc_bvh_info.restype = i32
     L.orc_bvh_info.argtypes = [vp, vp]
     L.orc_bvh_download.restype = i32
@@ -131,7 +133,13 @@ class OracleScene:
         if not self._bvh:
             if lib().orc_bvh_build(self._h) != 0:
                 raise RuntimeError("orc_bvh_build failed")
+            lib().orc_bvh_set_leaf_size(self._h, 0)     # the product's default leaf-range size
             self._bvh = True
+
+    def set_leaf_size(self, leaf_size):
+        """Leaf-range size used by the BVH-mode traversal counters (0 = product default)."""
+        self.build_bvh()
+        lib().orc_bvh_set_leaf_size(self._h, leaf_size)
 
     def camera_rays(self, Nx, Ny, sample=0):
         rays = np.empty(Nx * Ny, dtype=RAY_DTYPE)

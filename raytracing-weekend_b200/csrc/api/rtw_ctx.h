@@ -22,6 +22,7 @@ struct rtw_ctx {
     rtw::DScene scene{};
     rtw::LaunchCfg cfg{};
     int n_internal = 0;
+    int leaf_size = 1;
     float scene_min[3] = {0, 0, 0}, scene_max[3] = {0, 0, 0};
 
     // ---- wavefront pool ----
@@ -42,6 +43,7 @@ struct rtw_ctx {
     // ---- options ----
     long long opt_pool_paths = 1 << 21;
     int opt_top_nodes = 1024;
+    int opt_leaf_size = 0;          // 0 = auto (rtw_build_accel), else 1..32
     int opt_profile = 0;
     int opt_lag = 3;
 

@@ -140,8 +140,8 @@ extern "C" int rtw_bvh_download(rtw_ctx* c, uint64_t* morton, int32_t* leaf_prim
         auto dl = [](uint32_t ref) -> int32_t { return (ref & RTW_REF_LEAF) ? ~(int32_t)(ref & RTW_REF_MASK) : (int32_t)ref; };
         for (int i = 0; i < ni; i++) {
             const float4 n0 = nodes[4 * i], n1 = nodes[4 * i + 1], n2 = nodes[4 * i + 2], n3 = nodes[4 * i + 3];
-            if (left) left[i] = dl(f2u(n3.x));
-            if (right) right[i] = dl(f2u(n3.y));
+            if (left) left[i] = dl(f2u(n3.z));     // the Karras hierarchy (n3.xy are the collapsed traversal refs)
+            if (right) right[i] = dl(f2u(n3.w));
             if (bounds) {
                 float* b = bounds + (size_t)12 * i;
                 b[0] = n0.x; b[1] = n0.y; b[2] = n0.z; b[3] = n0.w; b[4] = n1.x; b[5] = n1.y;

@@ -110,20 +110,15 @@ RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, float
     const float tmin = r.tmin, tmax = r.tmax;
     if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
         const float k = b.x;
-        float t, pa, pb;
-        if (type == RTW_PRIM_RECT_X) {
-            t = (k - o.x) / d.x;
-            pa = o.y + t * d.y;
-            pb = o.z + t * d.z;
-        } else if (type == RTW_PRIM_RECT_Y) {
-            t = (k - o.y) / d.y;
-            pa = o.x + t * d.x;
-            pb = o.z + t * d.z;
-        } else {
-            t = (k - o.z) / d.z;
-            pa = o.x + t * d.x;
-            pb = o.y + t * d.y;
-        }
+        // one instruction stream for the three axes (selects, no branches):
+        //   X: t from x, (pa, pb) = (y, z);  Y: t from y, (x, z);  Z: t from z, (x, y)
+        const bool ax = type == RTW_PRIM_RECT_X, az = type == RTW_PRIM_RECT_Z;
+        const float on = ax ? o.x : (az ? o.z : o.y), dn = ax ? d.x : (az ? d.z : d.y);
+        const float o1 = ax ? o.y : o.x, d1 = ax ? d.y : d.x;
+        const float o2 = az ? o.y : o.z, d2 = az ? d.y : d.z;
+        const float t = (k - on) / dn;
+        const float pa = o1 + t * d1;
+        const float pb = o2 + t * d2;
         if (t > tmax || t < tmin) return false;
         if (pa < a.x || pa > a.y || pb < a.z || pb > a.w) return false;
         if (!(t >= tmin && t <= tmax)) return false;  // rejects NaN

@@ -7,13 +7,24 @@
 namespace rtw {
 
 // ---- child reference of a BVH node ---------------------------------------
-// bit 31: leaf (low 30 bits = leaf index, i.e. position in Morton order)
+// bit 31: leaf RANGE — bits 0..24 = first leaf index (position in Morton order),
+//         bits 25..29 = count - 1.  A subtree of the Karras hierarchy that spans at
+//         most `leaf_size` (<= 32) consecutive leaves is referenced as one range and
+//         its primitives are tested in a loop; count == 1 is the plain LBVH leaf.
 // bit 30: node lives in the shared-memory "top" table (low bits = top index)
 // else  : index into the global node array
 #define RTW_REF_LEAF 0x80000000u
 #define RTW_REF_TOP  0x40000000u
 #define RTW_REF_MASK 0x3fffffffu
 #define RTW_REF_NONE 0xffffffffu
+#define RTW_LEAF_FIRST_MASK 0x01ffffffu
+#define RTW_MAX_LEAF_SIZE 32
+#define RTW_MAX_PRIMS (1 << 25)
+RTW_HD uint32_t leaf_range_ref(int first, int count) {
+    return RTW_REF_LEAF | ((uint32_t)(count - 1) << 25) | (uint32_t)first;
+}
+RTW_HD uint32_t leaf_range_first(uint32_t ref) { return ref & RTW_LEAF_FIRST_MASK; }
+RTW_HD uint32_t leaf_range_count(uint32_t ref) { return ((ref >> 25) & 31u) + 1u; }
 
 // ---- primitive record: 2 x float4 per leaf, stored in leaf (Morton) order ----
 //   SPHERE         a = c.xyz r          b = -  -  -  meta

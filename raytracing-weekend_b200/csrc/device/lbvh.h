@@ -135,8 +135,10 @@ RTW_HD int lbvh_delta(const unsigned long long* k, int n, int i, int j) {
 }
 
 // Internal node i of the hierarchy over n >= 2 sorted keys.  Child refs use the
-// download convention: >= 0 internal node, < 0 → leaf ~ref.
-RTW_HD void karras_node(const unsigned long long* k, int n, int i, int& left, int& right) {
+// download convention: >= 0 internal node, < 0 → leaf ~ref.  The node spans the
+// leaves [lo, hi]; its left child spans [lo, gamma], its right child [gamma+1, hi].
+RTW_HD void karras_node(const unsigned long long* k, int n, int i, int& left, int& right, int& lo_out, int& gamma_out,
+                        int& hi_out) {
     const int d = (lbvh_delta(k, n, i, i + 1) - lbvh_delta(k, n, i, i - 1)) >= 0 ? 1 : -1;
     const int dmin = lbvh_delta(k, n, i, i - d);
     int lmax = 2;
@@ -156,10 +158,24 @@ RTW_HD void karras_node(const unsigned long long* k, int n, int i, int& left, in
     const int lo = i < j ? i : j, hi = i < j ? j : i;
     left = (lo == gamma) ? ~gamma : gamma;
     right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    lo_out = lo;
+    gamma_out = gamma;
+    hi_out = hi;
+}
+RTW_HD void karras_node(const unsigned long long* k, int n, int i, int& left, int& right) {
+    int lo, gamma, hi;
+    karras_node(k, n, i, left, right, lo, gamma, hi);
 }
 
 // Convert a download-convention ref into the traversal encoding of layout.h.
 RTW_HD uint32_t encode_ref(int ref) { return ref < 0 ? (RTW_REF_LEAF | (uint32_t)(~ref)) : (uint32_t)ref; }
+// Traversal ref of the child spanning leaves [first, last]: one leaf range when the
+// subtree holds at most leaf_size primitives, else the internal node itself.
+RTW_HD uint32_t traversal_ref(int karras_ref, int first, int last, int leaf_size) {
+    const int count = last - first + 1;
+    if (count <= leaf_size) return leaf_range_ref(first, count);
+    return (uint32_t)karras_ref;
+}
 
 // Pack primitive p (material type mt) into its two-float4 leaf record.
 RTW_HD void pack_prim(const rtw_prim& p, int mattype, float4& a, float4& b, float2& ext) {

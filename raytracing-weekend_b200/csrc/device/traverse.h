@@ -66,6 +66,12 @@ RTW_HD int leaf_prim_of(const DScene& sc, uint32_t leaf) {
 #endif
 }
 
+// Both traversals are "while-while" loops (Aila & Laine 2009): an inner loop over
+// internal nodes until the thread holds a leaf range, then an inner loop over the
+// primitives of that range.  Lanes of a warp therefore spend their time in the same
+// kind of work, and a scene that is a single range (<= leaf_size primitives, e.g. the
+// Cornell box) is walked by all 32 lanes in lockstep.
+
 // Closest hit: lexicographic minimum of (t, primitive index).
 template <class Mem, bool kStats>
 RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r, float& t_best, uint32_t& leaf_best,
@@ -78,20 +84,8 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
     float tb = r.tmax;
     uint32_t lb = RTW_REF_NONE;
     for (;;) {
-        if (cur & RTW_REF_LEAF) {
-            const uint32_t leaf = cur & RTW_REF_MASK;
-            float t;
-            if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, leaf, r, t)) {
-                bool better = !found || t < tb;
-                if (!better && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);
-                if (better) {
-                    found = true;
-                    tb = t;
-                    lb = leaf;
-                }
-            }
-        } else {
+        bool exhausted = false;
+        while (!(cur & RTW_REF_LEAF)) {
             float4 n0, n1, n2, n3;
             fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
             if (kStats) stats->nodes++;
@@ -103,10 +97,29 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
                 const bool left_first = tl <= tr;
                 if (sp < RTW_STACK) stack[sp++] = left_first ? cr : cl;
                 cur = left_first ? cl : cr;
-                continue;
+            } else if (hl) {
+                cur = cl;
+            } else if (hr) {
+                cur = cr;
+            } else {
+                if (sp == 0) { exhausted = true; break; }
+                cur = stack[--sp];
             }
-            if (hl) { cur = cl; continue; }
-            if (hr) { cur = cr; continue; }
+        }
+        if (exhausted) break;
+        const uint32_t first = leaf_range_first(cur), end = first + leaf_range_count(cur);
+        for (uint32_t leaf = first; leaf < end; leaf++) {
+            float t;
+            if (kStats) stats->prims++;
+            if (prim_candidate<Mem>(sc, leaf, r, t)) {
+                bool better = !found || t < tb;
+                if (!better && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);
+                if (better) {
+                    found = true;
+                    tb = t;
+                    lb = leaf;
+                }
+            }
         }
         if (sp == 0) break;
         cur = stack[--sp];
@@ -124,11 +137,8 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
     int sp = 0;
     uint32_t cur = sc.root;
     for (;;) {
-        if (cur & RTW_REF_LEAF) {
-            float t;
-            if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, cur & RTW_REF_MASK, r, t)) return true;
-        } else {
+        bool exhausted = false;
+        while (!(cur & RTW_REF_LEAF)) {
             float4 n0, n1, n2, n3;
             fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
             if (kStats) stats->nodes++;
@@ -139,10 +149,21 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
             if (hl && hr) {
                 if (sp < RTW_STACK) stack[sp++] = cr;
                 cur = cl;
-                continue;
+            } else if (hl) {
+                cur = cl;
+            } else if (hr) {
+                cur = cr;
+            } else {
+                if (sp == 0) { exhausted = true; break; }
+                cur = stack[--sp];
             }
-            if (hl) { cur = cl; continue; }
-            if (hr) { cur = cr; continue; }
+        }
+        if (exhausted) break;
+        const uint32_t first = leaf_range_first(cur), end = first + leaf_range_count(cur);
+        for (uint32_t leaf = first; leaf < end; leaf++) {
+            float t;
+            if (kStats) stats->prims++;
+            if (prim_candidate<Mem>(sc, leaf, r, t)) return true;
         }
         if (sp == 0) break;
         cur = stack[--sp];

@@ -43,6 +43,7 @@ struct BuildBuffers {
     float4* nodes;                  // 4 * n_internal
     float4* top_nodes;              // 4 * max_top
     int max_top;
+    int leaf_size;                  // subtrees of <= leaf_size primitives become one leaf range (1 = plain LBVH)
 };
 cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches);
 

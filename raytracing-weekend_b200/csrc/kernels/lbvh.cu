@@ -105,18 +105,22 @@ __global__ void __launch_bounds__(kThreads) k_pack_leaves(const rtw_prim* __rest
 __global__ void __launch_bounds__(kThreads) k_karras(const unsigned long long* __restrict__ keys, int n,
                                                       float4* __restrict__ nodes, int* __restrict__ parent,
                                                       int* __restrict__ leaf_parent, int* __restrict__ flags,
-                                                      int* __restrict__ top_index) {
+                                                      int* __restrict__ top_index, int leaf_size) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
-    int left, right;
-    karras_node(keys, n, i, left, right);
+    int left, right, lo, gamma, hi;
+    karras_node(keys, n, i, left, right, lo, gamma, hi);
     if (left < 0) leaf_parent[~left] = i; else parent[left] = i;
     if (right < 0) leaf_parent[~right] = i; else parent[right] = i;
     if (i == 0) parent[0] = -1;
     flags[i] = 0;
     top_index[i] = -1;
-    // children now, boxes at refit; n3.z keeps the download-convention refs recoverable
-    nodes[4 * i + 3] = make_float4(__uint_as_float(encode_ref(left)), __uint_as_float(encode_ref(right)), 0.f, 0.f);
+    // children now, boxes at refit.  n3.xy = traversal refs (subtrees of <= leaf_size
+    // primitives collapsed into one leaf range), n3.zw = the Karras hierarchy itself
+    // (refit, topology download).
+    nodes[4 * i + 3] = make_float4(__uint_as_float(traversal_ref(left, lo, gamma, leaf_size)),
+                                   __uint_as_float(traversal_ref(right, gamma + 1, hi, leaf_size)),
+                                   __uint_as_float(encode_ref(left)), __uint_as_float(encode_ref(right)));
 }
 
 // One-leaf scene: node 0 = (leaf 0, unreachable point box at +FLT_MAX).  An inverted
@@ -126,7 +130,8 @@ __global__ void k_single_leaf(const float4* leaf_mn, const float4* leaf_mx, floa
     nodes[0] = make_float4(mn.x, mn.y, mn.z, mx.x);
     nodes[1] = make_float4(mx.y, mx.z, RTW_FLT_MAX, RTW_FLT_MAX);
     nodes[2] = make_float4(RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX);
-    nodes[3] = make_float4(__uint_as_float(RTW_REF_LEAF | 0u), __uint_as_float(RTW_REF_LEAF | 0u), 0.f, 0.f);
+    nodes[3] = make_float4(__uint_as_float(RTW_REF_LEAF | 0u), __uint_as_float(RTW_REF_LEAF | 0u),
+                           __uint_as_float(RTW_REF_LEAF | 0u), __uint_as_float(RTW_REF_LEAF | 0u));
     parent[0] = -1;
     top_index[0] = -1;
 }
@@ -156,8 +161,8 @@ __global__ void __launch_bounds__(kThreads) k_refit(int n, const int* __restrict
         __threadfence();
         const float4 n3 = nodes[4 * cur + 3];
         float3 lmn, lmx, rmn, rmx;
-        child_box(__float_as_uint(n3.x), leaf_mn, leaf_mx, nodes, lmn, lmx);
-        child_box(__float_as_uint(n3.y), leaf_mn, leaf_mx, nodes, rmn, rmx);
+        child_box(__float_as_uint(n3.z), leaf_mn, leaf_mx, nodes, lmn, lmx);
+        child_box(__float_as_uint(n3.w), leaf_mn, leaf_mx, nodes, rmn, rmx);
         nodes[4 * cur + 0] = make_float4(lmn.x, lmn.y, lmn.z, lmx.x);
         nodes[4 * cur + 1] = make_float4(lmx.y, lmx.z, rmn.x, rmn.y);
         nodes[4 * cur + 2] = make_float4(rmn.z, rmx.x, rmx.y, rmx.z);
@@ -237,7 +242,8 @@ cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches
     } else {
         n_internal = n - 1;
         const int nbi = (n_internal + kThreads - 1) / kThreads;
-        k_karras<<<nbi, kThreads, 0, s>>>(b.keys[0], n, b.nodes, b.parent, b.leaf_parent, b.flags, b.top_index);
+        k_karras<<<nbi, kThreads, 0, s>>>(b.keys[0], n, b.nodes, b.parent, b.leaf_parent, b.flags, b.top_index,
+                                          b.leaf_size < 1 ? 1 : (b.leaf_size > RTW_MAX_LEAF_SIZE ? RTW_MAX_LEAF_SIZE : b.leaf_size));
         k_refit<<<nb, kThreads, 0, s>>>(n, b.leaf_parent, b.parent, b.flags, b.leaf_mn, b.leaf_mx, b.nodes);
         l += 2;
     }

@@ -36,7 +36,9 @@ struct Emu {
     float scene_min[3], scene_max[3];
 };
 
-extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top) {
+extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) {
+    if (leaf_size <= 0) leaf_size = d->n_prims <= 16 ? 16 : 4;   // same default as rtw_build_accel
+    if (leaf_size > RTW_MAX_LEAF_SIZE) leaf_size = RTW_MAX_LEAF_SIZE;
     Emu* e = new Emu();
     const int n = d->n_prims;
     e->prims.assign(d->prims, d->prims + n);
@@ -156,16 +158,17 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top) {
         e->nodes[0] = make_float4(mn.x, mn.y, mn.z, mx.x);
         e->nodes[1] = make_float4(mx.y, mx.z, RTW_FLT_MAX, RTW_FLT_MAX);
         e->nodes[2] = make_float4(RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX, RTW_FLT_MAX);
-        e->nodes[3] = make_float4(u2f(RTW_REF_LEAF), u2f(RTW_REF_LEAF), 0.f, 0.f);
+        e->nodes[3] = make_float4(u2f(RTW_REF_LEAF), u2f(RTW_REF_LEAF), u2f(RTW_REF_LEAF), u2f(RTW_REF_LEAF));
         e->left[0] = ~0; e->right[0] = ~0;
     } else {
         for (int i = 0; i < ni; i++) {
-            int l, r;
-            karras_node(e->keys.data(), n, i, l, r);
+            int l, r, lo, gamma, hi;
+            karras_node(e->keys.data(), n, i, l, r, lo, gamma, hi);
             e->left[i] = l; e->right[i] = r;
             if (l < 0) leaf_parent[~l] = i; else parent[l] = i;
             if (r < 0) leaf_parent[~r] = i; else parent[r] = i;
-            e->nodes[4 * i + 3] = make_float4(u2f(encode_ref(l)), u2f(encode_ref(r)), 0.f, 0.f);
+            e->nodes[4 * i + 3] = make_float4(u2f(traversal_ref(l, lo, gamma, leaf_size)), u2f(traversal_ref(r, gamma + 1, hi, leaf_size)),
+                                              u2f(encode_ref(l)), u2f(encode_ref(r)));
         }
         parent[0] = -1;
         auto child_box = [&](uint32_t ref, float3& mn, float3& mx) {
@@ -182,8 +185,8 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top) {
                 if (flags[cur]++ == 0) break;
                 const float4 n3 = e->nodes[4 * cur + 3];
                 float3 lmn, lmx, rmn, rmx;
-                child_box(f2u(n3.x), lmn, lmx);
-                child_box(f2u(n3.y), rmn, rmx);
+                child_box(f2u(n3.z), lmn, lmx);
+                child_box(f2u(n3.w), rmn, rmx);
                 e->nodes[4 * cur + 0] = make_float4(lmn.x, lmn.y, lmn.z, lmx.x);
                 e->nodes[4 * cur + 1] = make_float4(lmx.y, lmx.z, rmn.x, rmn.y);
                 e->nodes[4 * cur + 2] = make_float4(rmn.z, rmx.x, rmx.y, rmx.z);
@@ -224,7 +227,8 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top) {
     sc.n_leaves = n;
     sc.n_internal = ni;
     sc.n_top = (int)queue.size();
-    sc.root = sc.n_top > 0 ? RTW_REF_TOP : 0u;
+    if (n <= leaf_size) sc.root = leaf_range_ref(0, n);
+    else sc.root = sc.n_top > 0 ? RTW_REF_TOP : 0u;
     return e;
 }
 

@@ -38,7 +38,7 @@ def lib():
     L = C.CDLL(_LIB)
     vp, i32 = C.c_void_p, C.c_int
     L.emu_create.restype = vp
-    L.emu_create.argtypes = [vp, i32]
+    L.emu_create.argtypes = [vp, i32, i32]
     L.emu_destroy.argtypes = [vp]
     L.emu_bvh_download.argtypes = [vp] * 7
     L.emu_trace.argtypes = [vp, vp, i32, vp, vp, vp, vp]
@@ -57,8 +57,8 @@ def _ptr(a):
 
 
 class EmuScene:
-    def __init__(self, desc_ptr, n_prims, max_top=1024):
-        self._h = lib().emu_create(C.cast(desc_ptr, C.c_void_p), max_top)
+    def __init__(self, desc_ptr, n_prims, max_top=1024, leaf_size=0):
+        self._h = lib().emu_create(C.cast(desc_ptr, C.c_void_p), max_top, leaf_size)
         self.n = n_prims
 
     def close(self):

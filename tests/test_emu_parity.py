@@ -27,8 +27,11 @@ def test_rays_and_hits_bit_exact(rtw, orc, emu, sid, Nx, Ny):
     s = rtw.Scene(sid, Nx, Ny)
     n = s.desc.contents.n_prims
     o = orc.OracleScene(s.desc, n)
-    for max_top in (0, 5, 4096):     # no staging / partial staging / everything staged
-        e = emu.EmuScene(s.desc, n, max_top=max_top)
+    # no staging / partial staging / everything staged  x  plain LBVH leaves / leaf ranges of
+    # <= 4 / <= 32 primitives / the default (a <= 16-primitive scene is ONE range)
+    for max_top, leaf_size in ((0, 1), (5, 4), (4096, 32), (64, 0)):
+        e = emu.EmuScene(s.desc, n, max_top=max_top, leaf_size=leaf_size)
+        o.set_leaf_size(leaf_size)
         cam_o = o.camera_rays(Nx, Ny, 3)
         cam_e = e.camera_rays(Nx, Ny, 3)
         assert cam_o.tobytes() == cam_e.tobytes()
@@ -41,6 +44,9 @@ def test_rays_and_hits_bit_exact(rtw, orc, emu, sid, Nx, Ny):
         sh = rayset.shadow_rays_from(rays, h0, [278.0, 554.0, 279.5], 6000)
         a0, _ = o.trace_any(sh, 0)
         assert np.array_equal(a0, e.trace_any(sh))
+        # the oracle walking ITS mirror of the hierarchy (leaf ranges included) finds the same hits
+        h1, _ = o.trace_closest(rays, 1)
+        assert np.array_equal(h0, h1)
         e.close()
     s.close()
 

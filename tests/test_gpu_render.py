@@ -7,14 +7,15 @@ from rtw_types import SCENE_CASES
 
 pytestmark = pytest.mark.gpu
 
-# Tolerances (stated).  The device and glibc libm differ by <= 2 ulp in
-# sinf/cosf/logf/powf/atan2f/asinf, so a path can differ in the last bits and — rarely —
-# take a different branch.  Per path: relative 2e-4 on >= 99.5 % of the pixels at 1 spp.
-# Image: relMSE = mean((I-R)^2 / (R^2 + 1e-2)) <= 1e-3 (target of BASELINE.json) — measured
-# values are orders of magnitude below because both sides draw the SAME samples.
-PATH_RTOL = 2e-4
-PATH_FRACTION = 0.995
+# Tolerances (stated).  Every floating-point operation of the path is correctly
+# rounded on both sides (+ - * / sqrt fmaf; transcendental functions fixed by the arithmetic
+# contract, tests/test_detmath.py; -fmad=false / -ffp-contract=off), so ONE sample of a pixel is
+# the same bits on the GPU and in the oracle: 1 spp images are compared BIT-EXACT.  At spp > 1
+# the only freedom is the order of the fp32 atomic adds into the accumulator: per-pixel relative
+# 1e-5 (+1e-6 absolute) and relMSE = mean((I-R)^2 / (R^2 + 1e-2)) <= 1e-10 on same-sample images;
+# the BASELINE.json target relMSE <= 1e-3 vs a converged image is test_converged_image below.
 RELMSE_MAX = 1e-3
+RELMSE_SAME_SAMPLES = 1e-10
 
 
 def relmse(img, ref):
@@ -29,16 +30,12 @@ def test_one_spp_per_path_agreement(director, orc, sid, Nx, Ny):
     ref, c = o.render(Nx, Ny, 1, mode=1)
     out = director.renderFrame(1)
     lin = director.linear()
-    a, b = ref[..., :3], lin[..., :3]
-    tol = PATH_RTOL * np.maximum(np.abs(a).max(axis=2), 1.0)
-    frac = (np.abs(a - b).max(axis=2) <= tol).mean()
-    assert frac >= PATH_FRACTION, frac
+    assert np.array_equal(ref.view(np.uint32), lin.view(np.uint32)), "1 spp image differs from the oracle in some bit"
     assert np.all(lin[..., 3] == 1.0) and np.all(out[..., 3] == 1.0)
     st = director.stats()
     assert st["paths"] == Nx * Ny
-    # ray counts: identical up to the rare diverged paths
-    assert abs(st["rays_closest"] - c["rays_closest"]) <= 0.01 * c["rays_closest"] + 16
-    assert abs(st["rays_shadow"] - c["rays_shadow"]) <= 0.01 * c["rays_shadow"] + 16
+    # identical random walks → identical ray counts
+    assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
     assert st["kernel_launches"] > 0
     # gamma: out = sqrt(linear)
     assert np.allclose(out[..., :3], np.sqrt(np.maximum(lin[..., :3], 0)), rtol=1e-6, atol=1e-7)
@@ -55,9 +52,27 @@ def test_same_sample_images(director, orc, sid, Nx, Ny, spp):
     assert np.all(lin[..., 3] == spp)
     r = ref[..., :3] / spp
     e = relmse(lin[..., :3], r)
+    assert e <= RELMSE_SAME_SAMPLES, e
+    assert np.allclose(lin[..., :3], r, rtol=1e-5, atol=1e-6)
+
+
+def test_converged_image_relmse(director, orc):
+    """Tier 2 of BASELINE.json: the GPU image at high spp against a CONVERGED reference image
+    made by the oracle from DISJOINT samples (k = spp..2*spp-1), so agreement is statistical,
+    not sample-by-sample: relMSE <= 1e-3, and per pixel |I-R| <= 0.05 + 0.10*R on 99.5 % of pixels."""
+    Nx = Ny = 64
+    spp = 8192
+    director.init(Nx, Ny, spp)
+    director.createScene(0)
+    director.renderFrame(spp)
+    lin = director.linear()[..., :3]
+    o = orc.OracleScene(director.scene.desc, 13)
+    ref, _ = o.render(Nx, Ny, spp, mode=0, sample_first=spp)
+    r = ref[..., :3] / spp
+    e = relmse(lin, r)
     assert e <= RELMSE_MAX, e
-    assert e <= 1e-4, e      # same samples on both sides: far below the target
-    assert abs(lin[..., :3].mean() - r.mean()) <= 2e-3 * r.mean()
+    ok = np.abs(lin - r).max(axis=2) <= 0.05 + 0.10 * r.max(axis=2)
+    assert ok.mean() >= 0.995, ok.mean()
 
 
 def test_pool_size_and_lag_do_not_change_the_image(director, orc):
@@ -108,16 +123,21 @@ def test_c2_full_size_properties(director, orc):
     st = director.stats()
     assert st["paths"] == Nx * Ny * spp
     assert np.all(lin[..., 3] == spp) and np.isfinite(lin).all() and (lin[..., :3] >= 0).all()
-    # the oracle at 4 spp estimates the same image mean (same estimator)
+    # left wall is green-ish, right wall red-ish (scene sanity)
+    assert out[300, 560, 0] > out[300, 560, 1] and out[300, 40, 1] > out[300, 40, 0]
+    # the full-size frame at the oracle's pace: samples 0..3 of every pixel, brute-force oracle
+    # (no BVH on that side), must be the same image up to the atomic-add order, with the same
+    # number of rays; sample 0 alone must be the same bits
     o = orc.OracleScene(director.scene.desc, 13)
     ref, c = o.render(Nx, Ny, 4, mode=0)
-    m_ref = ref[..., :3].mean() / 4
-    assert abs(lin[..., :3].mean() - m_ref) <= 0.02 * m_ref
-    # rays per path agree with the oracle's counters
-    assert abs(st["rays_closest"] / st["paths"] - c["rays_closest"] / c["paths"]) < 0.02
-    assert abs(st["rays_shadow"] / st["paths"] - c["rays_shadow"] / c["paths"]) < 0.02
-    # left wall is green-ish, right wall red-ish (scene sanity)
-    assert out[300, 590, 0] > out[300, 590, 1] and out[300, 10, 1] > out[300, 10, 0]
+    director.renderFrame(4)
+    lin4 = director.linear()
+    st4 = director.stats()
+    assert np.allclose(lin4[..., :3], ref[..., :3] / 4, rtol=1e-5, atol=1e-6)
+    assert st4["rays_closest"] == c["rays_closest"] and st4["rays_shadow"] == c["rays_shadow"]
+    ref1, _ = o.render(Nx, Ny, 1, mode=0)
+    director.renderFrame(1)
+    assert np.array_equal(ref1.view(np.uint32), director.linear().view(np.uint32))
 
 
 def test_profile_option_reports_stage_times(director):
