@@ -24,7 +24,7 @@ static int ensure_wave(rtw_ctx* c, int P) {
     RTW_CUDA(c, dalloc(pool, &w.thr, P));
     RTW_CUDA(c, dalloc(pool, &w.rad, P));
     RTW_CUDA(c, dalloc(pool, &w.misc, P));
-    RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_COUNT * P));
+    RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_SLOTS * P));
     RTW_CUDA(c, dalloc(pool, &w.sh_o, P));
     RTW_CUDA(c, dalloc(pool, &w.sh_d, P));
     RTW_CUDA(c, dalloc(pool, &w.sh_c, P));
@@ -69,6 +69,17 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     st = rtw_stats{};
     st.build_ms = build_ms;
     RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
+    if (max_depth == 0 && total > 0) {   // no ray is ever traced: black samples, counted
+        RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, w.accum, &launches));
+        RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
+        RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+        float ms0 = 0.f;
+        cudaEventElapsedTime(&ms0, c->ev_begin, c->ev_end);
+        st.render_ms = ms0;
+        st.paths = total;
+        st.kernel_launches = launches;
+        return RTW_OK;
+    }
     RTW_CUDA(c, wavefront_init(c->stream, w, &launches));
     const int lag = c->opt_lag;
     uint64_t iter = 0;

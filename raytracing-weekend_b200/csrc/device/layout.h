@@ -100,13 +100,14 @@ struct DScene {
 #define RTW_Q_DIELECTRIC 2
 #define RTW_Q_ISOTROPIC  3
 #define RTW_Q_TERMINAL   4   // miss, diffuse light, normal material: path ends
-#define RTW_Q_COUNT      5
+#define RTW_Q_COUNT      5   // shading classes
+#define RTW_Q_REGEN      5   // slots whose path finished this iteration: flushed and refilled by k_regen
+#define RTW_Q_SLOTS      6   // queues allocated (RTW_Q_SLOTS * P slot indices)
 
 // counters[] layout (uint32 unless noted)
-#define RTW_C_QUEUE0     0                 // RTW_Q_COUNT queue lengths
-#define RTW_C_SHADOW     5                 // shadow queue length
-#define RTW_C_ALIVE      6                 // live paths after the last k_logic
-#define RTW_C_PAD        7
+#define RTW_C_QUEUE0     0                 // RTW_Q_SLOTS queue lengths (5 shading classes + regen)
+#define RTW_C_SHADOW     6                 // shadow queue length
+#define RTW_C_ALIVE      7                 // closest-hit rays traced by the last iteration (0 = frame done)
 #define RTW_C_NEXT_LO    8                 // uint64 next sample ordinal (two words)
 #define RTW_C_RAYS_LO    10                // uint64 closest-hit rays traced
 #define RTW_C_SHRAYS_LO  12                // uint64 shadow rays traced
@@ -120,7 +121,7 @@ struct DWave {
     float4* thr;        // throughput.xyz, path seed bits
     float4* rad;        // radiance sum .xyz, pixel index bits
     uint2*  misc;       // (depth | state << 8, ray-time seed)
-    uint32_t* queue;    // RTW_Q_COUNT * P slot indices
+    uint32_t* queue;    // RTW_Q_SLOTS * P slot indices
     float4* sh_o;       // shadow queue: origin.xyz, tmax
     float4* sh_d;       //               direction.xyz, slot bits
     float4* sh_c;       //               contribution.xyz, path seed bits

@@ -3,8 +3,8 @@
 // The reference runs one megakernel thread per pixel (raygen/raygen.cu:123-159:
 // seed, jitter, camera ray, `rayColor` loop, gamma, store).  Here that loop is cut
 // at every optixTraverse into stages over a pool of P path slots:
-//   logic/generate → traverse closest → shade (one queue per material) →
-//   traverse shadow → (next iteration)
+//   regenerate (flush finished paths, start new ones) → traverse closest →
+//   shade (one queue per material) → traverse shadow → (next iteration)
 // A path keeps the exact per-path RNG ledger of SURVEY.md §7b, so sample k of a
 // pixel is the same random walk as in the scalar formulation.
 //
@@ -118,8 +118,9 @@ struct ShadowOut {
 // __closesthit__radiance (shaders/closehit.cu:45-121) / __miss__Program
 // (miss/miss.cu:23-30) followed by the tail of the rayColor loop body
 // (raygen.cu:60-83: accumulate, continue/terminate, Russian roulette, depth++).
+// Returns true iff the path ended here (the slot goes to the regen queue).
 template <int kClass, class Mem>
-RTW_HD void shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh) {
+RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh) {
     sh.emit = false;
     const float4 ro = w.ray_o[slot];
     const float4 rd = w.ray_d[slot];
@@ -155,7 +156,7 @@ RTW_HD void shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         ra.x += add.x; ra.y += add.y; ra.z += add.z;
         w.rad[slot] = ra;
         w.misc[slot] = make_uint2(misc_pack(depth, RTW_ST_DEAD), lseed);
-        return;
+        return true;
     }
 
     RayW r;
@@ -224,6 +225,7 @@ RTW_HD void shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
     w.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
     w.rad[slot] = ra;
     w.misc[slot] = make_uint2(misc_pack(depth, state), lseed);
+    return state != RTW_ST_ALIVE;
 }
 
 // ---- stage 3: shadow rays ----------------------------------------------------

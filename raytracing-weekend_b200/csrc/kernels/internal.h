@@ -56,10 +56,11 @@ struct LaunchCfg {
     bool has_shadow;        // scene has lights → NEE stage runs
 };
 cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
-// One wavefront iteration: reset counters, logic, traverse, shade*, shadow.
+// One wavefront iteration: regen, reset counters, traverse, shade*, shadow.
 cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
                                 uint64_t* launches, cudaEvent_t* stage_events /* 5 or null */);
 cudaError_t wavefront_init(cudaStream_t s, const DWave& w, uint64_t* launches);
+cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches);
 cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
 
 // ---- test hooks --------------------------------------------------------------

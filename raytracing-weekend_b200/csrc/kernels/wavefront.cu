@@ -2,8 +2,8 @@
 //
 // One iteration of the pool (replaces one trip of the `rayColor` while-loop of
 // raygen/raygen.cu:36-84 for every live path at once):
-//   memset        queue/shadow/alive counters
-//   k_logic       flush finished paths into the accumulator, regenerate camera paths
+//   k_regen       flush the paths that finished last iteration (compact queue), start new camera paths
+//   memset        queue/shadow/in-flight counters
 //   k_traverse    closest-hit LBVH traversal + per-material queue compaction
 //   k_shade<c>    one kernel per material queue: BSDF, NEE sample, Russian roulette
 //   k_shadow      any-hit traversal of the NEE rays, adds unoccluded contributions
@@ -31,33 +31,44 @@ __device__ __forceinline__ void stage_top(const DScene& sc, float4* s_top) {
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_logic(const DScene sc, const DWave w) {
+// Warp-aggregated push of `slot` onto queue `cls` for the lanes where `pred` holds:
+// one ballot + one atomicAdd per warp.
+__device__ __forceinline__ void queue_push(const DWave& w, int cls, bool pred, uint32_t slot) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t mask = __ballot_sync(0xffffffffu, pred);
+    if (!mask) return;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_QUEUE0 + cls, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) w.queue[(size_t)cls * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
+}
+
+// Regeneration: the slots whose path finished in the previous iteration (a compact
+// queue, so every lane of a warp does the same work) are flushed into the accumulator
+// and restarted with the next sample ordinal (raygen.cu:129-135, :141-158).
+__global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t alive = 0;
-    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot - lane < (uint32_t)w.P; slot += stride) {
-        const bool in = slot < (uint32_t)w.P;
-        const bool free_slot = in && logic_flush(w, slot);
-        const uint32_t mask = __ballot_sync(0xffffffffu, free_slot);
-        bool live = in && !free_slot;
-        if (mask) {
-            const int leader = __ffs(mask) - 1;
-            unsigned long long base = 0;
-            if ((int)lane == leader) base = atomic_add_u64(w.counters + RTW_C_NEXT_LO, (unsigned long long)__popc(mask));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (free_slot) {
-                const unsigned long long ordinal = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
-                if (ordinal < w.total) {
-                    generate_path(sc, w, slot, ordinal);
-                    live = true;
-                }
-            }
+    const uint32_t n = w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+    const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i - lane < n; i += stride) {
+        const bool in = i < n;
+        uint32_t slot = 0;
+        if (in) {
+            slot = q[i];
+            logic_flush(w, slot);
         }
-        alive += live ? 1u : 0u;
+        const uint32_t mask = __ballot_sync(0xffffffffu, in);
+        const int leader = __ffs(mask) - 1;
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomic_add_u64(w.counters + RTW_C_NEXT_LO, (unsigned long long)__popc(mask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (in) {
+            const unsigned long long ordinal = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
+            if (ordinal < w.total) generate_path(sc, w, slot, ordinal);
+        }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) alive += __shfl_xor_sync(0xffffffffu, alive, o);
-    if (lane == 0 && alive) atomicAdd(w.counters + RTW_C_ALIVE, alive);
 }
 
 // ---------------------------------------------------------------------------
@@ -65,22 +76,12 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t lt = (1u << lane) - 1u;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot - lane < (uint32_t)w.P; slot += stride) {
         int cls = -1;
         if (slot < (uint32_t)w.P) cls = traverse_thread<MemGlobal>(sc, s_top, w, slot);
 #pragma unroll
-        for (int c = 0; c < RTW_Q_COUNT; c++) {
-            const uint32_t mask = __ballot_sync(0xffffffffu, cls == c);
-            if (mask) {
-                const int leader = __ffs(mask) - 1;
-                uint32_t base = 0;
-                if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_QUEUE0 + c, (uint32_t)__popc(mask));
-                base = __shfl_sync(0xffffffffu, base, leader);
-                if (cls == c) w.queue[(size_t)c * w.P + base + __popc(mask & lt)] = slot;
-            }
-        }
+        for (int c = 0; c < RTW_Q_COUNT; c++) queue_push(w, c, cls == c, slot);
     }
 }
 
@@ -95,7 +96,13 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const DWave w
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i - lane < n; i += stride) {
         ShadowOut sh;
         sh.emit = false;
-        if (i < n) shade_thread<kClass, MemGlobal>(sc, w, q[i], sh);
+        bool finished = false;
+        uint32_t slot = 0;
+        if (i < n) {
+            slot = q[i];
+            finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh);
+        }
+        queue_push(w, RTW_Q_REGEN, finished, slot);
         if (kClass == RTW_Q_LAMBERTIAN) {
             const uint32_t mask = __ballot_sync(0xffffffffu, sh.emit);
             if (mask) {
@@ -106,7 +113,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const DWave w
                 if (sh.emit) {
                     const uint32_t pos = base + __popc(mask & lt);
                     w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
-                    w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(q[i]));
+                    w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
                     w.sh_c[pos] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, __uint_as_float(sh.seed));
                 }
             }
@@ -119,6 +126,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const DWave w
         for (int c = 0; c < RTW_Q_COUNT; c++) rays += w.counters[RTW_C_QUEUE0 + c];
         atomic_add_u64(w.counters + RTW_C_RAYS_LO, rays);
         atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)w.counters[RTW_C_SHADOW]);
+        w.counters[RTW_C_ALIVE] = (uint32_t)rays;   // 0 ⇒ nothing left in flight: the host stops iterating
     }
 }
 
@@ -134,9 +142,19 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave 
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) k_wave_init(const DWave w) {
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < (uint32_t)w.P; slot += stride)
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < (uint32_t)w.P; slot += stride) {
         w.misc[slot] = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
-    if (blockIdx.x == 0 && threadIdx.x < RTW_C_WORDS) w.counters[threadIdx.x] = 0u;
+        w.queue[(size_t)RTW_Q_REGEN * w.P + slot] = slot;   // every slot is free: the first k_regen fills the pool
+    }
+    if (blockIdx.x == 0 && threadIdx.x < RTW_C_WORDS)
+        w.counters[threadIdx.x] = (threadIdx.x == RTW_C_QUEUE0 + RTW_Q_REGEN) ? (uint32_t)w.P : 0u;
+}
+
+// Depth limit 0: `while (depth < maxRayDepth)` (raygen.cu:36) never runs, every sample is
+// black; only the sample count reaches the accumulator.
+__global__ void __launch_bounds__(kBlock) k_add_count(int n, float count, float4* __restrict__ accum) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) accum[i].w += count;
 }
 
 // raygen/raygen.cu:144-158: sqrt gamma of the mean, alpha 1 (Q29)
@@ -242,7 +260,7 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
         e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
         if (e != cudaSuccess) return e;
     }
-    cfg->grid_logic = resident_grid(k_logic, 0, sms);
+    cfg->grid_logic = resident_grid(k_regen, 0, sms);
     cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
     cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
     cfg->grid_shade = resident_grid(k_shade<RTW_Q_LAMBERTIAN>, 0, sms);
@@ -258,11 +276,12 @@ cudaError_t wavefront_init(cudaStream_t s, const DWave& w, uint64_t* launches) {
 cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
                                 uint64_t* launches, cudaEvent_t* ev) {
     uint64_t l = 0;
+    if (ev) cudaEventRecord(ev[0], s);
+    k_regen<<<cfg.grid_logic, kBlock, 0, s>>>(sc, w);
+    l++;
+    // queue lengths (the regen queue just consumed included), shadow count, rays-in-flight
     cudaError_t e = cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 8, s);
     if (e != cudaSuccess) return e;
-    if (ev) cudaEventRecord(ev[0], s);
-    k_logic<<<cfg.grid_logic, kBlock, 0, s>>>(sc, w);
-    l++;
     if (ev) cudaEventRecord(ev[1], s);
     k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
     l++;
@@ -277,6 +296,12 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (cfg.has_shadow) { k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w); l++; }
     if (ev) cudaEventRecord(ev[4], s);
     if (launches) *launches += l;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches) {
+    k_add_count<<<(n_pixels + kBlock - 1) / kBlock, kBlock, 0, s>>>(n_pixels, (float)count, accum);
+    if (launches) *launches += 1;
     return cudaGetLastError();
 }
 

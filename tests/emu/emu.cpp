@@ -285,7 +285,7 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
     const DScene& sc = e->sc;
     std::vector<float4> ray_o(P), ray_d(P), thr(P), rad(P), sh_o(P), sh_d(P), sh_c(P);
     std::vector<uint2> hit(P), misc(P, make_uint2(0, 0));
-    std::vector<uint32_t> queue((size_t)RTW_Q_COUNT * P), counters(RTW_C_WORDS, 0);
+    std::vector<uint32_t> queue((size_t)RTW_Q_SLOTS * P), counters(RTW_C_WORDS, 0);
     DWave w{};
     w.ray_o = ray_o.data(); w.ray_d = ray_d.data(); w.hit = hit.data(); w.thr = thr.data(); w.rad = rad.data();
     w.misc = misc.data(); w.queue = queue.data(); w.sh_o = sh_o.data(); w.sh_d = sh_d.data(); w.sh_c = sh_c.data();
@@ -294,20 +294,23 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
     w.sample_first = sample_first; w.sample_stride = sample_stride;
     w.total = (unsigned long long)Nx * Ny * sample_count;
     unsigned long long next = 0, rays = 0, shrays = 0, iters = 0;
+    if (max_depth == 0) {   // k_add_count
+        for (int i = 0; i < Nx * Ny; i++) accum[4 * i + 3] += (float)sample_count;
+        if (stats) { stats[0] = 0; stats[1] = 0; stats[2] = 0; }
+        return 0;
+    }
+    uint32_t* regen = queue.data() + (size_t)RTW_Q_REGEN * P;
+    for (int slot = 0; slot < P; slot++) regen[slot] = (uint32_t)slot;   // k_wave_init
+    counters[RTW_C_QUEUE0 + RTW_Q_REGEN] = (uint32_t)P;
     for (;;) {
-        for (int c = 0; c < 8; c++) counters[c] = 0;
-        uint32_t alive = 0;
-        for (int slot = 0; slot < P; slot++) {  // k_logic
-            bool live = true;
-            if (logic_flush(w, slot)) {
-                live = false;
-                const unsigned long long ord = next++;
-                if (ord < w.total) { generate_path(sc, w, slot, ord); live = true; }
-            }
-            alive += live;
+        for (uint32_t i = 0; i < counters[RTW_C_QUEUE0 + RTW_Q_REGEN]; i++) {  // k_regen
+            const uint32_t slot = regen[i];
+            logic_flush(w, slot);
+            const unsigned long long ord = next++;
+            if (ord < w.total) generate_path(sc, w, slot, ord);
         }
+        for (int c = 0; c < 8; c++) counters[c] = 0;
         iters++;
-        if (alive == 0) break;
         for (int slot = 0; slot < P; slot++) {  // k_traverse
             const int cls = traverse_thread<MemGeneric>(sc, sc.top_nodes, w, slot);
             if (cls >= 0) queue[(size_t)cls * P + counters[cls]++] = slot;
@@ -316,13 +319,15 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
             for (uint32_t i = 0; i < counters[cls]; i++) {
                 const uint32_t slot = queue[(size_t)cls * P + i];
                 ShadowOut sh;
+                bool fin;
                 switch (cls) {
-                case RTW_Q_LAMBERTIAN: shade_thread<RTW_Q_LAMBERTIAN, MemGeneric>(sc, w, slot, sh); break;
-                case RTW_Q_METAL: shade_thread<RTW_Q_METAL, MemGeneric>(sc, w, slot, sh); break;
-                case RTW_Q_DIELECTRIC: shade_thread<RTW_Q_DIELECTRIC, MemGeneric>(sc, w, slot, sh); break;
-                case RTW_Q_ISOTROPIC: shade_thread<RTW_Q_ISOTROPIC, MemGeneric>(sc, w, slot, sh); break;
-                default: shade_thread<RTW_Q_TERMINAL, MemGeneric>(sc, w, slot, sh); break;
+                case RTW_Q_LAMBERTIAN: fin = shade_thread<RTW_Q_LAMBERTIAN, MemGeneric>(sc, w, slot, sh); break;
+                case RTW_Q_METAL: fin = shade_thread<RTW_Q_METAL, MemGeneric>(sc, w, slot, sh); break;
+                case RTW_Q_DIELECTRIC: fin = shade_thread<RTW_Q_DIELECTRIC, MemGeneric>(sc, w, slot, sh); break;
+                case RTW_Q_ISOTROPIC: fin = shade_thread<RTW_Q_ISOTROPIC, MemGeneric>(sc, w, slot, sh); break;
+                default: fin = shade_thread<RTW_Q_TERMINAL, MemGeneric>(sc, w, slot, sh); break;
                 }
+                if (fin) regen[counters[RTW_C_QUEUE0 + RTW_Q_REGEN]++] = slot;
                 if (sh.emit) {
                     const uint32_t pos = counters[RTW_C_SHADOW]++;
                     sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
@@ -334,6 +339,9 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
         }
         shrays += counters[RTW_C_SHADOW];
         for (uint32_t i = 0; i < counters[RTW_C_SHADOW]; i++) shadow_thread<MemGeneric>(sc, sc.top_nodes, w, i);  // k_shadow
+        uint32_t traced = 0;
+        for (int cls = 0; cls < RTW_Q_COUNT; cls++) traced += counters[cls];
+        if (traced == 0) break;   // nothing in flight (the regen pass above flushed the last finished paths)
     }
     if (stats) { stats[0] = rays; stats[1] = shrays; stats[2] = iters; }
     return 0;

@@ -60,8 +60,11 @@ def test_converged_image_relmse(director, orc):
     """Tier 2 of BASELINE.json: the GPU image at high spp against a CONVERGED reference image
     made by the oracle from DISJOINT samples (k = spp..2*spp-1), so agreement is statistical,
     not sample-by-sample: relMSE <= 1e-3, and per pixel |I-R| <= 0.05 + 0.10*R on 99.5 % of pixels."""
-    Nx = Ny = 64
-    spp = 8192
+    # The reference's estimator is noisy (Q7/Q10: no pdf ratio in the throughput, caustics through
+    # the glass sphere): two independent 8192 spp images still differ by relMSE 3e-3 (measured), so
+    # "converged" here means 65536 spp on both sides (expected relMSE ~4e-4 between them).
+    Nx = Ny = 40
+    spp = 65536
     director.init(Nx, Ny, spp)
     director.createScene(0)
     director.renderFrame(spp)

@@ -77,15 +77,19 @@ def test_top_staging_sizes_give_identical_hits(director, rtw, orc):
     Nx, Ny = 96, 96
     director.init(Nx, Ny, 1)
     ref = None
-    for top in (0, 7, 512, 3584):
+    # staged-node count x leaf-range size (1 = plain LBVH: every internal node is reachable)
+    for top, leaf in ((0, 1), (7, 1), (512, 1), (3584, 1), (0, 4), (7, 8), (3584, 4), (1024, 32), (1024, 0)):
         director.set_option("top_nodes", top)
+        director.set_option("leaf_size", leaf)
         director.createScene(4)
-        assert director.bvh_info().n_top == min(top, 3409)
+        n_top = director.bvh_info().n_top
+        assert n_top == min(top, 3409) if leaf == 1 else 0 <= n_top <= min(top, 3409)
         hits = director.trace_closest(director.camera_rays(0))
         if ref is None:
             ref = hits
         assert np.array_equal(ref, hits)
     director.set_option("top_nodes", 1024)
+    director.set_option("leaf_size", 0)
 
 
 def test_full_size_ray_set_cornell(director, rtw, orc):
