@@ -78,9 +78,19 @@ RTW_HD bool hit_boundary_sphere(float3 direction, float3 origin, float3 center, 
     return false;
 }
 
+// The world ray carried through an instance transform, remembered between the
+// primitives of one traversal: consecutive leaves mostly share their instance (the six
+// faces of a box, the 1000 small spheres of scene 4), so the 3x4 product is done once
+// per run of equal transform ids instead of once per primitive.  Same values either way.
+struct XfRay {
+    int xf;        // transform id of (o, d); -1 = nothing cached
+    float3 o, d;
+};
+
 // Object-space ray of the primitive (a, b, meta).
 template <class Mem>
-RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, const RayW& r, float3& o, float3& d) {
+RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, const RayW& r, XfRay& cache, float3& o,
+                       float3& d) {
     const int type = meta_type(meta);
     o = r.o;
     d = r.d;
@@ -89,10 +99,15 @@ RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, cons
     } else {
         const int xf = meta_xform(meta);
         if (xf >= 0) {
-            const float4* m = sc.xforms + 6 * xf;
-            float4 r0 = Mem::ld4(m), r1 = Mem::ld4(m + 1), r2 = Mem::ld4(m + 2);
-            o = xform_point(r0, r1, r2, r.o);
-            d = xform_vector(r0, r1, r2, r.d);
+            if (xf != cache.xf) {
+                const float4* m = sc.xforms + 6 * xf;
+                float4 r0 = Mem::ld4(m), r1 = Mem::ld4(m + 1), r2 = Mem::ld4(m + 2);
+                cache.o = xform_point(r0, r1, r2, r.o);
+                cache.d = xform_vector(r0, r1, r2, r.d);
+                cache.xf = xf;
+            }
+            o = cache.o;
+            d = cache.d;
         }
     }
 }
@@ -100,13 +115,13 @@ RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, cons
 // True (and the accepted distance) iff leaf `leaf` reports an intersection that
 // optixReportIntersection would accept for ray r.
 template <class Mem>
-RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, float& t_out) {
+RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, XfRay& cache, float& t_out) {
     const float4 a = Mem::ld4(sc.prims + 2 * leaf);
     const float4 b = Mem::ld4(sc.prims + 2 * leaf + 1);
     const uint32_t meta = f2u(b.w);
     const int type = meta_type(meta);
     float3 o, d;
-    object_ray<Mem>(sc, a, b, meta, r, o, d);
+    object_ray<Mem>(sc, a, b, meta, r, cache, o, d);
     const float tmin = r.tmin, tmax = r.tmax;
     if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
         const float k = b.x;
@@ -202,7 +217,9 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
     const uint32_t meta = f2u(b.w);
     const int type = meta_type(meta);
     float3 o, d;
-    object_ray<Mem>(sc, a, b, meta, r, o, d);
+    XfRay cache;
+    cache.xf = -1;
+    object_ray<Mem>(sc, a, b, meta, r, cache, o, d);
     const int xf = (type == RTW_PRIM_MOVING_SPHERE) ? -1 : meta_xform(meta);
     float4 w0, w1, w2, q0, q1, q2;  // world→object rows, object→world rows
     if (xf >= 0) {

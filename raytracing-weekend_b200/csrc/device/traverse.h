@@ -76,7 +76,10 @@ RTW_HD int leaf_prim_of(const DScene& sc, uint32_t leaf) {
 template <class Mem, bool kStats>
 RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r, float& t_best, uint32_t& leaf_best,
                              TravStats* stats) {
-    const SlabRay sr = make_slab_ray(r);
+    SlabRay sr;
+    if (!(sc.root & RTW_REF_LEAF)) sr = make_slab_ray(r);   // a single-range scene never tests a box
+    XfRay xfc;
+    xfc.xf = -1;
     uint32_t stack[RTW_STACK];
     int sp = 0;
     uint32_t cur = sc.root;
@@ -111,15 +114,12 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
         for (uint32_t leaf = first; leaf < end; leaf++) {
             float t;
             if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, leaf, r, t)) {
-                bool better = !found || t < tb;
-                if (!better && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);
-                if (better) {
-                    found = true;
-                    tb = t;
-                    lb = leaf;
-                }
-            }
+            const bool hit = prim_candidate<Mem>(sc, leaf, r, xfc, t);
+            bool better = hit && (!found || t < tb);
+            if (hit && found && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);   // rare tie
+            found = found || hit;
+            tb = better ? t : tb;
+            lb = better ? leaf : lb;
         }
         if (sp == 0) break;
         cur = stack[--sp];
@@ -132,7 +132,10 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
 // Any hit (shadow rays): true iff some primitive reports an accepted hit in [tmin, tmax].
 template <class Mem, bool kStats>
 RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, TravStats* stats) {
-    const SlabRay sr = make_slab_ray(r);
+    SlabRay sr;
+    if (!(sc.root & RTW_REF_LEAF)) sr = make_slab_ray(r);
+    XfRay xfc;
+    xfc.xf = -1;
     uint32_t stack[RTW_STACK];
     int sp = 0;
     uint32_t cur = sc.root;
@@ -163,7 +166,7 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
         for (uint32_t leaf = first; leaf < end; leaf++) {
             float t;
             if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, leaf, r, t)) return true;
+            if (prim_candidate<Mem>(sc, leaf, r, xfc, t)) return true;
         }
         if (sp == 0) break;
         cur = stack[--sp];

@@ -3,7 +3,7 @@
 // One iteration of the pool (replaces one trip of the `rayColor` while-loop of
 // raygen/raygen.cu:36-84 for every live path at once):
 //   k_regen       flush the paths that finished last iteration (compact queue), start new camera paths
-//   memset        queue/shadow/in-flight counters
+//   k_advance     retire the sample ordinals just handed out, clear the per-iteration counters
 //   k_traverse    closest-hit LBVH traversal + per-material queue compaction
 //   k_shade<c>    one kernel per material queue: BSDF, NEE sample, Russian roulette
 //   k_shadow      any-hit traversal of the NEE rays, adds unoccluded contributions
@@ -48,27 +48,29 @@ __device__ __forceinline__ void queue_push(const DWave& w, int cls, bool pred, u
 // queue, so every lane of a warp does the same work) are flushed into the accumulator
 // and restarted with the next sample ordinal (raygen.cu:129-135, :141-158).
 __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w) {
-    const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n = w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+    const unsigned long long next = *reinterpret_cast<const unsigned long long*>(w.counters + RTW_C_NEXT_LO);
     const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i - lane < n; i += stride) {
-        const bool in = i < n;
-        uint32_t slot = 0;
-        if (in) {
-            slot = q[i];
-            logic_flush(w, slot);
-        }
-        const uint32_t mask = __ballot_sync(0xffffffffu, in);
-        const int leader = __ffs(mask) - 1;
-        unsigned long long base = 0;
-        if ((int)lane == leader) base = atomic_add_u64(w.counters + RTW_C_NEXT_LO, (unsigned long long)__popc(mask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (in) {
-            const unsigned long long ordinal = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
-            if (ordinal < w.total) generate_path(sc, w, slot, ordinal);
-        }
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t slot = q[i];
+        logic_flush(w, slot);
+        // queue position i takes sample ordinal next + i: no atomic (k_advance moves `next` on by n
+        // after this kernel)
+        const unsigned long long ordinal = next + (unsigned long long)i;
+        if (ordinal < w.total) generate_path(sc, w, slot, ordinal);
     }
+}
+
+// Between k_regen and k_traverse: the sample ordinals handed out by k_regen are retired and the
+// per-iteration counters (queue lengths, shadow count, rays in flight) are cleared.
+__global__ void k_advance(const DWave w) {
+    if (threadIdx.x == 0) {
+        unsigned long long* next = reinterpret_cast<unsigned long long*>(w.counters + RTW_C_NEXT_LO);
+        *next += (unsigned long long)w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+    }
+    __syncwarp();
+    if (threadIdx.x < 8) w.counters[threadIdx.x] = 0u;
 }
 
 // ---------------------------------------------------------------------------
@@ -80,8 +82,15 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot - lane < (uint32_t)w.P; slot += stride) {
         int cls = -1;
         if (slot < (uint32_t)w.P) cls = traverse_thread<MemGlobal>(sc, s_top, w, slot);
-#pragma unroll
-        for (int c = 0; c < RTW_Q_COUNT; c++) queue_push(w, c, cls == c, slot);
+        __syncwarp();   // rays leave the traversal loops at different times: reconverge before the warp-wide push
+        // one atomic round trip per warp for ALL classes: the lanes of a class elect a leader,
+        // the (up to five) leaders issue their atomicAdd in the same instruction
+        const uint32_t peers = __match_any_sync(0xffffffffu, cls);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if (cls >= 0 && (int)lane == leader) base = atomicAdd(w.counters + RTW_C_QUEUE0 + cls, (uint32_t)__popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (cls >= 0) w.queue[(size_t)cls * w.P + base + __popc(peers & ((1u << lane) - 1u))] = slot;
     }
 }
 
@@ -279,9 +288,8 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (ev) cudaEventRecord(ev[0], s);
     k_regen<<<cfg.grid_logic, kBlock, 0, s>>>(sc, w);
     l++;
-    // queue lengths (the regen queue just consumed included), shadow count, rays-in-flight
-    cudaError_t e = cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 8, s);
-    if (e != cudaSuccess) return e;
+    k_advance<<<1, 32, 0, s>>>(w);
+    l++;
     if (ev) cudaEventRecord(ev[1], s);
     k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
     l++;
