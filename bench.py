@@ -271,27 +271,52 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD if spp == SPP else WORKLOAD.replace("1024 spp", "%d spp (override)" % spp),
                            "parallelism": "sample-sharded x%d, one NCCL reduce per frame" % world,
-                           "l2_policy": "inputs larger than L2: the wavefront pool (2^21 paths x ~150 B state + queues = ~310 MB) "
+                           "l2_policy": "inputs larger than L2: the wavefront pool (2^21 path slots x 152 B state + queues = 319 MB) "
                                         "streams through HBM every iteration, no flush between steps",
                            "wall_ms_per_step": wall / args.steps * 1e3},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},
                 "gpu_launches": int(tot[2].item()), "clocks": clk.summary()}
         # ---- roofline of the dominant kernel: k_traverse (closest-hit traversal) ----
-        # algorithmic bytes/ray from the ORACLE's visit counters on the host-mirror LBVH
+        # HBM-visible ALGORITHMIC bytes per ray: misc 8 + ray_o 16 + ray_d 16 read,
+        # hit 8 + queue entry 4 written = 52 B.  The BVH nodes / primitive records of SURVEY.md §8d
+        # (64 B x nodes + 32 B x primitives, +48 B per transformed run) are served by L1 / shared memory
+        # for this scene; they are reported beside it from the ORACLE's visit counters on its mirror
+        # of the hierarchy, not from the GPU.
         s2, o2 = oracle_scene(rtw)
         _, c = o2.render(NX, NY, 1, DEPTH, n_threads=host_cores(), mode=1)
         s2.close()
         rc = max(c["rays_closest"], 1)
-        bytes_per_ray = (64.0 * c["nodes_closest"] + 32.0 * (c["prims_closest"] - c["prims_xf_closest"]) +
-                         80.0 * c["prims_xf_closest"]) / rc + 96.0
+        onchip_per_ray = (64.0 * c["nodes_closest"] + 32.0 * (c["prims_closest"] - c["prims_xf_closest"]) +
+                          80.0 * c["prims_xf_closest"]) / rc
+        hbm_per_ray = 52.0
+        iters = max(agg["iters"], 1)
         trav_s = agg["trav_ms"] * 1e-3
-        achieved = agg["rays"] * bytes_per_ray / max(trav_s, 1e-9) / 1e9
+        achieved = agg["rays"] * hbm_per_ray / max(trav_s, 1e-9) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from the committed ncu capture
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("k_traverse_dram_bytes_per_launch")
+        # per-stage picture of one wavefront iteration (HBM-visible algorithmic bytes per unit)
+        n_paths = float(NX * NY * spp) * args.steps / world
+        stages = {}
+        for name, ms, units, bpu in (("k_traverse", agg["trav_ms"], agg["rays"], 52.0),
+                                     ("k_shade*", agg["shade_ms"], agg["rays"], 156.0 + 48.0 * agg["shrays"] / max(agg["rays"], 1)),
+                                     ("k_shadow", agg["shadow_ms"], agg["shrays"], 72.0),
+                                     ("k_regen", agg["logic_ms"], n_paths, 116.0)):
+            gbs = units * bpu / max(ms * 1e-3, 1e-9) / 1e9
+            stages[name] = {"ms_per_iteration": ms / iters, "units_per_iteration": units / iters, "bytes_per_unit": bpu,
+                            "gbs": gbs, "frac": gbs / peak, "share_of_render": ms / max(agg["render_ms"], 1e-9)}
         line["roofline"] = {"bound": "hbm", "kernel": "k_traverse", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                            "bytes_per_ray": bytes_per_ray, "rays_per_launch": agg["rays"] / max(agg["iters"], 1),
-                            "avg_launch_ms": agg["trav_ms"] / max(agg["iters"], 1),
-                            "stage_share": {k: agg[k] / max(agg["render_ms"], 1e-9) for k in ("trav_ms", "shadow_ms", "shade_ms", "logic_ms")}}
+                            "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                            "bytes_per_ray": hbm_per_ray, "rays_per_launch": agg["rays"] / iters,
+                            "avg_launch_ms": agg["trav_ms"] / iters,
+                            "on_chip_bytes_per_ray_survey_8d": onchip_per_ray + 96.0,
+                            "on_chip_gbs": agg["rays"] * onchip_per_ray / max(trav_s, 1e-9) / 1e9,
+                            "note": "k_traverse is instruction-issue bound, not HBM bound (profiles/): the 13-primitive "
+                                    "scene is one leaf range read through L1; frac is the share of HBM peak its mandatory "
+                                    "state stream uses",
+                            "stages": stages}
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = cpu_sample(rtw, 15.0)
             line["cpu_baseline"] = cb
