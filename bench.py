@@ -159,6 +159,7 @@ def main():
     import torch
     import torch.distributed as dist
     rtw = importlib.import_module("raytracing-weekend_b200")
+    sharding = importlib.import_module("raytracing-weekend_b200.sharding")
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -172,7 +173,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     spp = args.spp
     # rank g renders samples k = g (mod world): counts differ by at most one
-    my_count = len(range(rank, spp, world))
+    my_first, my_stride, my_count = sharding.shard_samples(spp, rank, world)
 
     d = rtw.Director(local)
     d.init(NX, NY, spp)
@@ -199,13 +200,11 @@ def main():
 
     def frame(count_stats):
         """One frame with the scene resident: zero, render my samples, reduce, tonemap on root."""
-        accum.zero_()
-        torch.cuda.synchronize()
-        d.render_accum(accum.data_ptr(), rank, world, my_count, DEPTH)
+        sharding.render_frame_sharded(lambda f, sd, n: d.render_accum(accum.data_ptr(), f, sd, n, DEPTH),
+                                      accum, spp, rank, world)
         st = d.stats()
         n_l = st["kernel_launches"] + 1
         if world > 1:
-            dist.reduce(accum, dst=0)
             torch.cuda.synchronize()
         if rank == 0:
             d.tonemap(accum.data_ptr(), out.data_ptr(), spp)

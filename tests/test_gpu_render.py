@@ -102,10 +102,13 @@ def test_sample_sharding_matches_single_render(director, rtw):
     director.createScene(0)
     director.renderFrame(8)
     whole = director.linear()
+    import importlib
+    sharding = importlib.import_module("raytracing-weekend_b200.sharding")
     acc = torch.zeros(Ny, Nx, 4, device="cuda:0")
     torch.cuda.synchronize()
     for g in range(2):
-        director.render_accum(acc.data_ptr(), g, 2, 4)
+        first, stride, count = sharding.shard_samples(8, g, 2)
+        director.render_accum(acc.data_ptr(), first, stride, count)
     out = torch.empty_like(acc)
     director.tonemap(acc.data_ptr(), out.data_ptr(), 8)
     torch.cuda.synchronize()
