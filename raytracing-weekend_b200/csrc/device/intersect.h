@@ -131,7 +131,14 @@ RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, XfRay
         const float on = ax ? o.x : (az ? o.z : o.y), dn = ax ? d.x : (az ? d.z : d.y);
         const float o1 = ax ? o.y : o.x, d1 = ax ? d.y : d.x;
         const float o2 = az ? o.y : o.z, d2 = az ? d.y : d.z;
-        const float t = (k - on) / dn;
+        // A path leaving a rect has its origin ON that plane about half of the time, so k - on is
+        // exactly 0 for one primitive per ray; 0 / dn would take the division's out-of-line slow path
+        // (zero numerator) on a few lanes in every iteration.  0 * (+-1) is the same value: +-0 with the
+        // quotient's sign, NaN when dn is 0 or NaN.
+        const float num = k - on;
+        float t;
+        if (num == 0.0f) t = num * ((dn > 0.0f || dn < 0.0f) ? copysignf(1.0f, dn) : NAN);
+        else t = num / dn;
         const float pa = o1 + t * d1;
         const float pb = o2 + t * d2;
         if (t > tmax || t < tmin) return false;

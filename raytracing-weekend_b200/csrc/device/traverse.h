@@ -114,12 +114,15 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
         for (uint32_t leaf = first; leaf < end; leaf++) {
             float t;
             if (kStats) stats->prims++;
-            const bool hit = prim_candidate<Mem>(sc, leaf, r, xfc, t);
-            bool better = hit && (!found || t < tb);
-            if (hit && found && t == tb) better = leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb);   // rare tie
-            found = found || hit;
-            tb = better ? t : tb;
-            lb = better ? leaf : lb;
+            if (prim_candidate<Mem>(sc, leaf, r, xfc, t)) {
+                if (!found || t < tb) {
+                    found = true;
+                    tb = t;
+                    lb = leaf;
+                } else if (t == tb && leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb)) {   // rare tie: lower primitive id wins
+                    lb = leaf;
+                }
+            }
         }
         if (sp == 0) break;
         cur = stack[--sp];
