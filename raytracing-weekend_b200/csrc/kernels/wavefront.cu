@@ -5,7 +5,7 @@
 //   k_regen       flush the paths that finished last iteration (compact queue), start new camera paths
 //   k_advance     retire the sample ordinals just handed out, clear the per-iteration counters
 //   k_traverse    closest-hit LBVH traversal + per-material queue compaction
-//   k_shade<c>    one kernel per material queue: BSDF, NEE sample, Russian roulette
+//   k_shade_all   the five material queues in one launch, one BSDF per CTA chunk: BSDF, NEE sample, Russian roulette
 //   k_shadow      any-hit traversal of the NEE rays, adds unoccluded contributions
 // Queue pushes are warp-aggregated: one ballot + one atomicAdd per warp and class,
 // so every warp of a shading kernel runs exactly one BSDF.
@@ -95,46 +95,65 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
 }
 
 // ---------------------------------------------------------------------------
+// One 256-wide chunk [i0, i0 + 256) of shading queue kClass: every warp runs ONE BSDF.
 template <int kClass>
-__global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const DWave w) {
+__device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, uint32_t i0, uint32_t n) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t lt = (1u << lane) - 1u;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t n = w.counters[RTW_C_QUEUE0 + kClass];
+    const uint32_t i = i0 + threadIdx.x;
     const uint32_t* q = w.queue + (size_t)kClass * w.P;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i - lane < n; i += stride) {
-        ShadowOut sh;
-        sh.emit = false;
-        bool finished = false;
-        uint32_t slot = 0;
-        if (i < n) {
-            slot = q[i];
-            finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh);
-        }
-        queue_push(w, RTW_Q_REGEN, finished, slot);
-        if (kClass == RTW_Q_LAMBERTIAN) {
-            const uint32_t mask = __ballot_sync(0xffffffffu, sh.emit);
-            if (mask) {
-                const int leader = __ffs(mask) - 1;
-                uint32_t base = 0;
-                if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_SHADOW, (uint32_t)__popc(mask));
-                base = __shfl_sync(0xffffffffu, base, leader);
-                if (sh.emit) {
-                    const uint32_t pos = base + __popc(mask & lt);
-                    w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
-                    w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
-                    w.sh_c[pos] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, __uint_as_float(sh.seed));
-                }
+    ShadowOut sh;
+    sh.emit = false;
+    bool finished = false;
+    uint32_t slot = 0;
+    if (i < n) {
+        slot = q[i];
+        finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh);
+    }
+    __syncwarp();
+    queue_push(w, RTW_Q_REGEN, finished, slot);
+    if (kClass == RTW_Q_LAMBERTIAN) {
+        const uint32_t mask = __ballot_sync(0xffffffffu, sh.emit);
+        if (mask) {
+            const int leader = __ffs(mask) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_SHADOW, (uint32_t)__popc(mask));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (sh.emit) {
+                const uint32_t pos = base + __popc(mask & ((1u << lane) - 1u));
+                w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
+                w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
+                w.sh_c[pos] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, __uint_as_float(sh.seed));
             }
         }
     }
-    if (kClass == RTW_Q_TERMINAL && blockIdx.x == 0 && threadIdx.x == 0) {
-        // ray statistics of this iteration: every queued slot was one closest-hit ray,
-        // every shadow-queue entry one any-hit ray (all shading kernels ran before this one)
+}
+
+// All five shading queues in ONE launch.  The queues are cut into 256-entry chunks, numbered
+// class by class (lambertian first: the long queue starts first, the short ones fill the tail);
+// CTAs take chunks round-robin, so a CTA — and every warp in it — runs one BSDF at a time.  The
+// short queues (metal, dielectric, terminal: 5-30 % of the vertices) no longer pay a launch each
+// with the machine mostly idle.
+__global__ void __launch_bounds__(kBlock, 2) k_shade_all(const DScene sc, const DWave w, uint32_t class_mask) {
+    uint32_t n[RTW_Q_COUNT], first_chunk[RTW_Q_COUNT + 1];
+    first_chunk[0] = 0;
+#pragma unroll
+    for (int c = 0; c < RTW_Q_COUNT; c++) {
+        n[c] = (class_mask >> c) & 1u ? w.counters[RTW_C_QUEUE0 + c] : 0u;
+        first_chunk[c + 1] = first_chunk[c] + (n[c] + kBlock - 1) / kBlock;
+    }
+    for (uint32_t v = blockIdx.x; v < first_chunk[RTW_Q_COUNT]; v += gridDim.x) {
+        if (v < first_chunk[1]) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, (v - first_chunk[0]) * kBlock, n[0]);
+        else if (v < first_chunk[2]) shade_chunk<RTW_Q_METAL>(sc, w, (v - first_chunk[1]) * kBlock, n[1]);
+        else if (v < first_chunk[3]) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, (v - first_chunk[2]) * kBlock, n[2]);
+        else if (v < first_chunk[4]) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, (v - first_chunk[3]) * kBlock, n[3]);
+        else shade_chunk<RTW_Q_TERMINAL>(sc, w, (v - first_chunk[4]) * kBlock, n[4]);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // ray statistics of this iteration: every queued slot was one closest-hit ray (the shadow
+        // rays are counted by k_shadow, once the shadow queue is complete)
         unsigned long long rays = 0;
         for (int c = 0; c < RTW_Q_COUNT; c++) rays += w.counters[RTW_C_QUEUE0 + c];
         atomic_add_u64(w.counters + RTW_C_RAYS_LO, rays);
-        atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)w.counters[RTW_C_SHADOW]);
         w.counters[RTW_C_ALIVE] = (uint32_t)rays;   // 0 ⇒ nothing left in flight: the host stops iterating
     }
 }
@@ -146,6 +165,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave 
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n = w.counters[RTW_C_SHADOW];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) shadow_thread<MemGlobal>(sc, s_top, w, i);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
 }
 
 // ---------------------------------------------------------------------------
@@ -272,7 +292,7 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
     cfg->grid_logic = resident_grid(k_regen, 0, sms);
     cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
     cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
-    cfg->grid_shade = resident_grid(k_shade<RTW_Q_LAMBERTIAN>, 0, sms);
+    cfg->grid_shade = resident_grid(k_shade_all, 0, sms);
     return cudaSuccess;
 }
 
@@ -294,11 +314,7 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
     l++;
     if (ev) cudaEventRecord(ev[2], s);
-    if (cfg.class_mask & (1u << RTW_Q_LAMBERTIAN)) { k_shade<RTW_Q_LAMBERTIAN><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w); l++; }
-    if (cfg.class_mask & (1u << RTW_Q_METAL)) { k_shade<RTW_Q_METAL><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w); l++; }
-    if (cfg.class_mask & (1u << RTW_Q_DIELECTRIC)) { k_shade<RTW_Q_DIELECTRIC><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w); l++; }
-    if (cfg.class_mask & (1u << RTW_Q_ISOTROPIC)) { k_shade<RTW_Q_ISOTROPIC><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w); l++; }
-    k_shade<RTW_Q_TERMINAL><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w);
+    k_shade_all<<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, cfg.class_mask | (1u << RTW_Q_TERMINAL));
     l++;
     if (ev) cudaEventRecord(ev[3], s);
     if (cfg.has_shadow) { k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w); l++; }
