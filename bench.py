@@ -143,6 +143,7 @@ def run_reference(args):
 
 
 def main():
+    global NX, NY, SCENE, WORKLOAD
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -150,8 +151,16 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--spp", type=int, default=SPP, help="override for quick checks (not the benchmark config)")
     ap.add_argument("--pool", type=int, default=0, help="wavefront pool size override")
+    ap.add_argument("--scene", type=int, default=SCENE, help="override for profiling other configs (not the benchmark config)")
+    ap.add_argument("--nx", type=int, default=NX)
+    ap.add_argument("--ny", type=int, default=NY)
+    ap.add_argument("--leaf-size", type=int, default=0)
+    ap.add_argument("--opt", action="append", default=[], help="name=value passed to rtw_set_option (tuning runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if (args.scene, args.nx, args.ny) != (SCENE, NX, NY):
+        SCENE, NX, NY = args.scene, args.nx, args.ny
+        WORKLOAD = "OVERRIDE (not the benchmark config): scene %d, %dx%d, 1024 spp, depth 20" % (SCENE, NX, NY)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -177,10 +186,18 @@ def main():
 
     d = rtw.Director(local)
     d.init(NX, NY, spp)
+    if args.leaf_size:
+        d.set_option("leaf_size", args.leaf_size)
+    for kv in args.opt:             # build-time options (walker, leaf_size, top_nodes) must precede createScene
+        k, v = kv.split("=")
+        d.set_option(k, int(v))
     d.createScene(SCENE)
     if args.pool:
         d.set_option("pool_paths", args.pool)
     d.set_option("profile", 1)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        d.set_option(k, int(v))
     scene_desc = d.scene.desc
     dsc = scene_desc.contents
     import ctypes as C

@@ -101,6 +101,15 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "leaf_size")) {
         if (value < 0 || value > RTW_MAX_LEAF_SIZE) return fail(c, RTW_ERR_INVALID, "leaf_size out of range [0, 32]");
         c->opt_leaf_size = (int)value;
+    } else if (!strcmp(name, "step_nodes") || !strcmp(name, "step_prims") || !strcmp(name, "min_active")) {
+        if (value < 1 || value > 1024) return fail(c, RTW_ERR_INVALID, "walk option out of range [1, 1024]");
+        if (name[0] == 'm') c->opt_min_active = (int)(value > 32 ? 32 : value);
+        else if (name[5] == 'n') c->opt_step_nodes = (int)value;
+        else c->opt_step_prims = (int)value;
+        c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;
+    } else if (!strcmp(name, "walker")) {
+        if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "walker out of range [-1, 1]");
+        c->opt_walker = (int)value;
     } else if (!strcmp(name, "profile")) {
         c->opt_profile = value ? 1 : 0;
     } else if (!strcmp(name, "lag")) {
@@ -369,8 +378,17 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     if (n <= b.leaf_size) sc.root = leaf_range_ref(0, n);
     else sc.root = sc.n_top > 0 ? (RTW_REF_TOP | 0u) : 0u;
     c->n_internal = ni;
+    // Traversal variant (tools/sweep_walk.sh, B200, 64 spp): persistent walkers win on the deep
+    // hierarchy of the Book-2 scene (3410 primitives: k_traverse 0.77 -> 0.60 ms per 2 M rays) but
+    // lose ~10 % on the 520-528 primitive scenes, where rays finish within a few steps of each other and
+    // the finish-order queue pushes cost the shading kernels their slot-order coalescing.
+    c->cfg.walker = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 1024);
     RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
     c->cfg.class_mask = c->class_mask;
+    c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;
+    if (sc.root & RTW_REF_LEAF) {   // one leaf range: every ray does the same walk, nothing to rebalance
+        c->cfg.step_nodes = 1; c->cfg.step_prims = RTW_MAX_LEAF_SIZE; c->cfg.min_active = 0;   // static mode
+    }
     c->cfg.has_shadow = (sc.n_lights > 0 && sc.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN)));
     c->accel_built = true;
     return RTW_OK;

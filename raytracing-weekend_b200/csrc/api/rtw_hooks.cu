@@ -26,9 +26,11 @@ static int trace_common(rtw_ctx* c, const rtw_ray* rays, int n, rtw_hit* hits, i
     RTW_CUDA(c, dalloc(t.pool, &d_rays, n));
     if (hits) RTW_CUDA(c, dalloc(t.pool, &d_hits, n));
     if (occ) RTW_CUDA(c, dalloc(t.pool, &d_occ, n));
+    uint32_t* d_work = nullptr;
+    RTW_CUDA(c, dalloc(t.pool, &d_work, 2));
     RTW_CUDA(c, cudaMemcpyAsync(d_rays, rays, sizeof(rtw_ray) * n, cudaMemcpyHostToDevice, c->stream));
     uint64_t l = 0;
-    RTW_CUDA(c, launch_trace(c->stream, c->scene, c->cfg, d_rays, n, d_hits, d_occ, &l));
+    RTW_CUDA(c, launch_trace(c->stream, c->scene, c->cfg, d_rays, n, d_hits, d_occ, d_work, &l));
     if (hits) RTW_CUDA(c, cudaMemcpyAsync(hits, d_hits, sizeof(rtw_hit) * n, cudaMemcpyDeviceToHost, c->stream));
     if (occ) RTW_CUDA(c, cudaMemcpyAsync(occ, d_occ, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
     RTW_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -112,7 +112,9 @@ struct DScene {
 #define RTW_C_RAYS_LO    10                // uint64 closest-hit rays traced
 #define RTW_C_SHRAYS_LO  12                // uint64 shadow rays traced
 #define RTW_C_PATHS_LO   14                // uint64 paths flushed
-#define RTW_C_WORDS      16
+#define RTW_C_WORK_CLOSEST 16              // next pool slot to fetch (persistent traversal warps)
+#define RTW_C_WORK_SHADOW  17              // next shadow-queue entry to fetch
+#define RTW_C_WORDS      20
 
 struct DWave {
     float4* ray_o;      // origin.xyz, ray time

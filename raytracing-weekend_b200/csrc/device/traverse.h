@@ -178,3 +178,94 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
 }
 
 }  // namespace rtw
+
+// ---------------------------------------------------------------------------
+// Resumable traversal ("walker"): the same walk as traverse_closest / traverse_any, cut
+// into steps so that a persistent warp can (i) bound how long its lanes run apart — at
+// most max_nodes node visits, then at most max_prims primitive tests per step — and
+// (ii) hand a finished lane a new ray while the others are still walking (dynamic ray
+// fetching, Aila & Laine 2009).  The result does not depend on the step sizes: closest
+// hit is the lexicographic minimum of (t, primitive id), any hit is an existence test.
+namespace rtw {
+
+template <class Mem, bool kAny>
+struct Walker {
+    RayW r;
+    SlabRay sr;
+    XfRay xfc;
+    uint32_t cur;        // reference to process next (valid when no range is in progress)
+    uint32_t li, lend;   // leaf range in progress: [li, lend); li == lend → none
+    int sp;
+    float tb;            // closest: best t so far (culling limit); any: r.tmax
+    uint32_t lb;
+    bool found, done;
+    // the stack lives OUTSIDE the struct (a dynamically indexed member would force every field
+    // of the walker into local memory); the caller owns `uint32_t stack[RTW_STACK]`
+
+    RTW_HD void begin(const DScene& sc, const RayW& ray) {
+        r = ray;
+        if (!(sc.root & RTW_REF_LEAF)) sr = make_slab_ray(r);
+        xfc.xf = -1;
+        cur = sc.root;
+        li = lend = 0;
+        sp = 0;
+        tb = r.tmax;
+        lb = RTW_REF_NONE;
+        found = false;
+        done = false;
+    }
+
+    RTW_HD void pop(const uint32_t* stack) {
+        if (sp == 0) done = true;
+        else cur = stack[--sp];
+    }
+
+    RTW_HD void step(const DScene& sc, const float4* top, uint32_t* stack, int max_nodes, int max_prims) {
+        int n = 0;
+        while (!done && li == lend && !(cur & RTW_REF_LEAF) && n < max_nodes) {
+            float4 n0, n1, n2, n3;
+            fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
+            float tl, tr;
+            const bool hl = slab_test(sr, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, r.tmin, tb, tl);
+            const bool hr = slab_test(sr, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.tmin, tb, tr);
+            const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
+            if (hl && hr) {
+                const bool left_first = kAny || tl <= tr;
+                if (sp < RTW_STACK) stack[sp++] = left_first ? cr : cl;
+                cur = left_first ? cl : cr;
+            } else if (hl) {
+                cur = cl;
+            } else if (hr) {
+                cur = cr;
+            } else {
+                pop(stack);
+            }
+            n++;
+        }
+        if (!done && li == lend && (cur & RTW_REF_LEAF)) {
+            li = leaf_range_first(cur);
+            lend = li + leaf_range_count(cur);
+        }
+        int p = 0;
+        while (!done && li < lend && p < max_prims) {
+            float t;
+            if (prim_candidate<Mem>(sc, li, r, xfc, t)) {
+                if (kAny) {
+                    found = true;
+                    done = true;
+                } else if (!found || t < tb) {
+                    found = true;
+                    tb = t;
+                    lb = li;
+                } else if (t == tb && leaf_prim_of(sc, li) < leaf_prim_of(sc, lb)) {
+                    lb = li;
+                }
+            }
+            li++;
+            p++;
+            if (!done && li == lend) pop(stack);   // range consumed
+        }
+    }
+};
+
+}  // namespace rtw

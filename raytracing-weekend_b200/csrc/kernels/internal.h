@@ -54,6 +54,8 @@ struct LaunchCfg {
     size_t smem_top;        // bytes of shared memory for the staged top nodes
     uint32_t class_mask;    // which shading queues the scene can populate
     bool has_shadow;        // scene has lights → NEE stage runs
+    int step_nodes, step_prims, min_active;   // persistent traversal: step bounds, refill threshold
+    bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
 };
 cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
 // One wavefront iteration: regen, reset counters, traverse, shade*, shadow.
@@ -65,7 +67,7 @@ cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* 
 
 // ---- test hooks --------------------------------------------------------------
 cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg, const rtw_ray* rays, int n,
-                         rtw_hit* hits, int32_t* occluded, uint64_t* launches);
+                         rtw_hit* hits, int32_t* occluded, uint32_t* work2 /* 2 device words */, uint64_t* launches);
 cudaError_t launch_rng_stream(cudaStream_t s, uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out,
                               uint32_t* lcg_out, float* rnd_out, uint32_t* xs_out, float* randf_out);
 cudaError_t launch_math_eval(cudaStream_t s, int fn, const float* x, const float* y, int n, float* out);

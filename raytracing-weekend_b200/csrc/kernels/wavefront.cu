@@ -71,18 +71,206 @@ __global__ void k_advance(const DWave w) {
     }
     __syncwarp();
     if (threadIdx.x < 8) w.counters[threadIdx.x] = 0u;
+    if (threadIdx.x == 8) w.counters[RTW_C_WORK_CLOSEST] = 0u;   // work counters of the persistent traversal warps
+    if (threadIdx.x == 9) w.counters[RTW_C_WORK_SHADOW] = 0u;
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWave w) {
+// Persistent traversal warps with dynamic ray fetching.
+//
+// A warp keeps 32 walkers (device/traverse.h).  All lanes advance by one bounded step
+// (<= kStepNodes node visits, then <= kStepPrims primitive tests), so lanes never run
+// further apart than one step; a lane whose ray is finished parks its result, and as soon
+// as fewer than kMinActive lanes are still walking the warp (converged at that point)
+// publishes the parked results with one aggregated push and refills the idle lanes from a
+// global work counter.  Incoherent rays (after the first bounce every ray of a warp is in
+// a different part of the hierarchy) otherwise leave most lanes waiting for the longest
+// walk of the warp: ncu measured 8.3 of 32 lanes active on the Book-2 scene before this.
+struct WalkCfg {
+    int step_nodes, step_prims, min_active;
+    // min_active <= 0: static mode — every ray does the same walk (the scene is one leaf range), so
+    // warp k simply takes items 32k.., 32(k + #warps).. and no work counter is touched
+};
+
+// Job = where rays come from and where results go.
+struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-54)
+    static constexpr bool kAny = false;
+    const DScene& sc;
+    const DWave& w;
+    __device__ uint32_t count() const { return (uint32_t)w.P; }
+    __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_CLOSEST; }
+    __device__ bool load(uint32_t slot, RayW& r) const {
+        const uint2 m = w.misc[slot];
+        if (misc_state(m.x) != RTW_ST_ALIVE) return false;
+        const float4 ro = w.ray_o[slot];
+        const float4 rd = w.ray_d[slot];
+        r.o = f3(ro);
+        r.d = f3(rd);
+        r.tmin = 1e-6f;
+        r.tmax = 1.e27f;   // shaders/appconfig.h:3
+        r.time = ro.w;
+        r.gather = rd.w;
+        r.seed = sc.has_media ? f2u(w.thr[slot].w) : 0u;
+        return true;
+    }
+    // returns the shading class of the finished slot
+    __device__ int store(uint32_t slot, bool found, float t, uint32_t leaf) const {
+        w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
+        if (!found) return RTW_Q_TERMINAL;
+        const int mt = meta_mattype(f2u(__ldg(sc.prims + 2 * leaf + 1).w));
+        if (mt == RTW_MAT_LAMBERTIAN) return RTW_Q_LAMBERTIAN;
+        if (mt == RTW_MAT_METAL) return RTW_Q_METAL;
+        if (mt == RTW_MAT_DIELECTRIC) return RTW_Q_DIELECTRIC;
+        if (mt == RTW_MAT_ISOTROPIC) return RTW_Q_ISOTROPIC;
+        return RTW_Q_TERMINAL;
+    }
+};
+
+struct ShadowJob {       // stage 3: the NEE rays (closehit.cu:16-42,97-113): tmin 500e-7, ray time 0
+    static constexpr bool kAny = true;
+    const DScene& sc;
+    const DWave& w;
+    __device__ uint32_t count() const { return w.counters[RTW_C_SHADOW]; }
+    __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_SHADOW; }
+    __device__ bool load(uint32_t i, RayW& r) const {
+        const float4 so = w.sh_o[i];
+        const float4 sd = w.sh_d[i];
+        r.o = f3(so);
+        r.d = f3(sd);
+        r.tmin = 500 * 1.0e-7f;
+        r.tmax = so.w;
+        r.time = 0.0f;
+        r.gather = sc.has_motion ? w.ray_d[f2u(sd.w)].w : 0.f;
+        r.seed = f2u(w.sh_c[i].w);
+        return true;
+    }
+    __device__ int store(uint32_t i, bool occluded, float, uint32_t) const {
+        if (!occluded) {
+            const float4 c = w.sh_c[i];
+            const uint32_t slot = f2u(w.sh_d[i].w);
+            float4 ra = w.rad[slot];
+            ra.x += c.x; ra.y += c.y; ra.z += c.z;
+            w.rad[slot] = ra;
+        }
+        return -1;
+    }
+};
+
+struct TraceJob {        // test hook: caller-supplied rays (rtw_trace_closest / rtw_trace_any)
+    const DScene& sc;
+    const rtw_ray* rays;
+    int n;
+    rtw_hit* hits;
+    int32_t* occluded;
+    uint32_t* counter;
+    __device__ uint32_t count() const { return (uint32_t)n; }
+    __device__ uint32_t* work() const { return counter; }
+    __device__ bool load(uint32_t i, RayW& r) const {
+        const rtw_ray a = rays[i];
+        r.o = f3(a.origin[0], a.origin[1], a.origin[2]);
+        r.d = f3(a.dir[0], a.dir[1], a.dir[2]);
+        r.tmin = a.tmin; r.tmax = a.tmax; r.time = a.time; r.gather = a.gather_time; r.seed = a.seed;
+        return true;
+    }
+};
+struct TraceClosestJob : TraceJob {
+    static constexpr bool kAny = false;
+    __device__ int store(uint32_t i, bool found, float t, uint32_t leaf) const {
+        rtw_hit h;
+        h.t = found ? t : 0.f;
+        h.prim = found ? sc.leaf_prim[leaf] : -1;
+        hits[i] = h;
+        return -1;
+    }
+};
+struct TraceAnyJob : TraceJob {
+    static constexpr bool kAny = true;
+    __device__ int store(uint32_t i, bool found, float, uint32_t) const {
+        occluded[i] = found ? 1 : 0;
+        return -1;
+    }
+};
+
+template <class Job, bool kPush>
+__device__ __forceinline__ void walk_persistent(const DScene& sc, const DWave* wq, const float4* s_top, const Job& job,
+                                                const WalkCfg wc) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t total = job.count();
+    Walker<MemGlobal, Job::kAny> wk;
+    uint32_t stack[RTW_STACK];
+    wk.done = true;
+    bool active = false;
+    uint32_t item = 0;
+    int parked_cls = -1;         // shading class of a finished slot waiting for the aggregated push
+    uint32_t parked_slot = 0;
+    const bool static_work = wc.min_active <= 0;
+    uint32_t static_base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
+    const uint32_t static_stride = gridDim.x * blockDim.x;
+    for (;;) {
+        // ---- converged: publish parked results, refill idle lanes ----
+        if (kPush) {
+            const uint32_t peers = __match_any_sync(0xffffffffu, parked_cls);
+            const int leader = __ffs(peers) - 1;
+            uint32_t base = 0;
+            if (parked_cls >= 0 && (int)lane == leader)
+                base = atomicAdd(wq->counters + RTW_C_QUEUE0 + parked_cls, (uint32_t)__popc(peers));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (parked_cls >= 0) wq->queue[(size_t)parked_cls * wq->P + base + __popc(peers & lt)] = parked_slot;
+            parked_cls = -1;
+        }
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        uint32_t base = 0;
+        if (static_work) {
+            base = static_base;
+            static_base += static_stride;
+        } else {
+            if (lane == 0) base = atomicAdd(job.work(), (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        if (!active) {
+            const uint32_t idx = base + __popc(idle & lt);
+            if (idx < total) {
+                RayW r;
+                if (job.load(idx, r)) {
+                    wk.begin(sc, r);
+                    active = true;
+                    item = idx;
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (base >= total) break;   // nothing walking, nothing left to fetch
+            continue;                   // the fetched items needed no traversal (empty slots): fetch again
+        }
+        // ---- walk until too few lanes are still busy (or, once the work is gone, until all are done) ----
+        const int min_active = (!static_work && base + 32u <= total) ? wc.min_active : 1;
+        do {
+            if (active) {
+                wk.step(sc, s_top, stack, wc.step_nodes, wc.step_prims);
+                if (wk.done) {
+                    const int cls = job.store(item, wk.found, wk.tb, wk.lb);
+                    if (kPush) { parked_cls = cls; parked_slot = item; }
+                    active = false;
+                }
+            }
+            __syncwarp();
+        } while (__popc(__ballot_sync(0xffffffffu, active)) >= min_active);
+    }
+}
+
+// Flat variant for scenes that are ONE leaf range (<= leaf_size primitives, e.g. the Cornell box):
+// every ray walks the same primitive list, so lanes stay in lockstep by construction and the
+// straight-line per-thread traversal (device/traverse.h) beats the resumable walker by ~20 %.
+__global__ void __launch_bounds__(kBlock) k_traverse_flat(const DScene sc, const DWave w) {
     extern __shared__ float4 s_top[];
-    stage_top(sc, s_top);
+    if (!(sc.root & RTW_REF_LEAF)) stage_top(sc, s_top);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot - lane < (uint32_t)w.P; slot += stride) {
         int cls = -1;
         if (slot < (uint32_t)w.P) cls = traverse_thread<MemGlobal>(sc, s_top, w, slot);
-        __syncwarp();   // rays leave the traversal loops at different times: reconverge before the warp-wide push
+        __syncwarp();
         // one atomic round trip per warp for ALL classes: the lanes of a class elect a leader,
         // the (up to five) leaders issue their atomicAdd in the same instruction
         const uint32_t peers = __match_any_sync(0xffffffffu, cls);
@@ -92,6 +280,22 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
         base = __shfl_sync(0xffffffffu, base, leader);
         if (cls >= 0) w.queue[(size_t)cls * w.P + base + __popc(peers & ((1u << lane) - 1u))] = slot;
     }
+}
+
+__global__ void __launch_bounds__(kBlock) k_shadow_flat(const DScene sc, const DWave w) {
+    extern __shared__ float4 s_top[];
+    if (!(sc.root & RTW_REF_LEAF)) stage_top(sc, s_top);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n = w.counters[RTW_C_SHADOW];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) shadow_thread<MemGlobal>(sc, s_top, w, i);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
+}
+
+__global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWave w, const WalkCfg wc) {
+    extern __shared__ float4 s_top[];
+    stage_top(sc, s_top);
+    const ClosestJob job{sc, w};
+    walk_persistent<ClosestJob, true>(sc, &w, s_top, job, wc);
 }
 
 // ---------------------------------------------------------------------------
@@ -159,13 +363,13 @@ __global__ void __launch_bounds__(kBlock, 2) k_shade_all(const DScene sc, const 
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave w) {
+__global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave w, const WalkCfg wc) {
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t n = w.counters[RTW_C_SHADOW];
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) shadow_thread<MemGlobal>(sc, s_top, w, i);
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
+    const ShadowJob job{sc, w};
+    walk_persistent<ShadowJob, false>(sc, nullptr, s_top, job, wc);
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)w.counters[RTW_C_SHADOW]);
 }
 
 // ---------------------------------------------------------------------------
@@ -196,25 +400,17 @@ __global__ void __launch_bounds__(kBlock) k_tonemap(int n, float inv_spp, const 
 
 // ---- test hooks --------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) k_trace(const DScene sc, const rtw_ray* __restrict__ rays, int n,
-                                                   rtw_hit* __restrict__ hits, int32_t* __restrict__ occluded) {
+                                                   rtw_hit* __restrict__ hits, int32_t* __restrict__ occluded,
+                                                   uint32_t* __restrict__ work /* two zeroed words */, const WalkCfg wc) {
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
-    const int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const rtw_ray a = rays[i];
-        RayW r;
-        r.o = f3(a.origin[0], a.origin[1], a.origin[2]);
-        r.d = f3(a.dir[0], a.dir[1], a.dir[2]);
-        r.tmin = a.tmin; r.tmax = a.tmax; r.time = a.time; r.gather = a.gather_time; r.seed = a.seed;
-        if (hits) {
-            float t; uint32_t leaf;
-            const bool found = traverse_closest<MemGlobal, false>(sc, s_top, r, t, leaf, nullptr);
-            rtw_hit h;
-            h.t = found ? t : 0.f;
-            h.prim = found ? sc.leaf_prim[leaf] : -1;
-            hits[i] = h;
-        }
-        if (occluded) occluded[i] = traverse_any<MemGlobal, false>(sc, s_top, r, nullptr) ? 1 : 0;
+    if (hits) {
+        const TraceClosestJob job{{sc, rays, n, hits, occluded, work}};
+        walk_persistent<TraceClosestJob, false>(sc, nullptr, s_top, job, wc);
+    }
+    if (occluded) {
+        const TraceAnyJob job{{sc, rays, n, hits, occluded, work + 1}};
+        walk_persistent<TraceAnyJob, false>(sc, nullptr, s_top, job, wc);
     }
 }
 
@@ -288,10 +484,19 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_traverse_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_shadow_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
+        if (e != cudaSuccess) return e;
     }
     cfg->grid_logic = resident_grid(k_regen, 0, sms);
-    cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
-    cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
+    if (!cfg->walker) {
+        cfg->grid_traverse = resident_grid(k_traverse_flat, cfg->smem_top, sms);
+        cfg->grid_shadow = resident_grid(k_shadow_flat, cfg->smem_top, sms);
+    } else {
+        cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
+        cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
+    }
     cfg->grid_shade = resident_grid(k_shade_all, 0, sms);
     return cudaSuccess;
 }
@@ -311,13 +516,18 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     k_advance<<<1, 32, 0, s>>>(w);
     l++;
     if (ev) cudaEventRecord(ev[1], s);
-    k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
+    if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
+    else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
     l++;
     if (ev) cudaEventRecord(ev[2], s);
     k_shade_all<<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, cfg.class_mask | (1u << RTW_Q_TERMINAL));
     l++;
     if (ev) cudaEventRecord(ev[3], s);
-    if (cfg.has_shadow) { k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w); l++; }
+    if (cfg.has_shadow) {
+        if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
+        else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
+        l++;
+    }
     if (ev) cudaEventRecord(ev[4], s);
     if (launches) *launches += l;
     return cudaGetLastError();
@@ -337,11 +547,13 @@ cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* 
 }
 
 cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg, const rtw_ray* rays, int n,
-                         rtw_hit* hits, int32_t* occluded, uint64_t* launches) {
+                         rtw_hit* hits, int32_t* occluded, uint32_t* work2, uint64_t* launches) {
     if (n <= 0) return cudaSuccess;
     int grid = (n + kBlock - 1) / kBlock;
     if (grid > cfg.grid_traverse) grid = cfg.grid_traverse;
-    k_trace<<<grid, kBlock, cfg.smem_top, s>>>(sc, rays, n, hits, occluded);
+    cudaError_t e = cudaMemsetAsync(work2, 0, 2 * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    k_trace<<<grid, kBlock, cfg.smem_top, s>>>(sc, rays, n, hits, occluded, work2, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
     if (launches) *launches += 1;
     return cudaGetLastError();
 }

@@ -154,3 +154,31 @@ def test_profile_option_reports_stage_times(director):
     st = director.stats()
     director.set_option("profile", 0)
     assert st["traverse_ms"] > 0 and st["shade_ms"] > 0 and st["logic_ms"] > 0
+
+
+@pytest.mark.parametrize("sid,Nx,Ny", [(1, 96, 54), (4, 64, 64)])
+def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
+    """Flat per-thread traversal kernels vs persistent walkers with dynamic ray fetching, and
+    several step / refill settings: the 1 spp image stays bit-exact (closest hit is the minimum
+    of (t, primitive id), independent of the order rays and nodes are visited in)."""
+    director.init(Nx, Ny, 1)
+    ref = None
+    try:
+        for opts in ({"walker": 0}, {"walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
+                     {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1}):
+            for k, v in opts.items():
+                director.set_option(k, v)
+            director.createScene(sid)
+            if ref is None:
+                o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+                ref, c = o.render(Nx, Ny, 1, mode=1)
+            director.renderFrame(1)
+            assert np.array_equal(ref.view(np.uint32), director.linear().view(np.uint32)), opts
+            st = director.stats()
+            assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+            hits = director.trace_closest(director.camera_rays(0))
+            rh, _ = o.trace_closest(director.camera_rays(0), 1)
+            assert np.array_equal(hits, rh)
+    finally:
+        for k, v in {"walker": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
+            director.set_option(k, v)
