@@ -265,8 +265,10 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
         if (meta_flip(meta)) n = -n;
         if (xf >= 0) n = xform_normal(w0, w1, w2, n);
         h.normal = normalize(n);
-        h.u = (pa - a.x) / (a.y - a.x);
-        h.v = (pb - a.z) / (a.w - a.z);
+        if (want_uv) {   // (u, v) only feed image textures (texture/imageTexture.cu:15); checker and noise use the point
+            h.u = (pa - a.x) / (a.y - a.x);
+            h.v = (pb - a.z) / (a.w - a.z);
+        }
     } else {  // volumes: normal (1,0,0), uv 0 (volumeBox.cu:88-93, volumeSphere.cu:99-105)
         float3 n = f3(1.f, 0.f, 0.f);
         if (xf >= 0) n = xform_normal(w0, w1, w2, n);

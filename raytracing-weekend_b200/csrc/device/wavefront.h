@@ -126,7 +126,8 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
     const float4 rd = w.ray_d[slot];
     const uint2 hit = w.hit[slot];
     const float4 th = w.thr[slot];
-    float4 ra = w.rad[slot];
+    float4 ra = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (kClass == RTW_Q_TERMINAL) ra = w.rad[slot];   // the scattering classes touch the sum only in the rare case below
     const uint2 m = w.misc[slot];
     uint32_t depth = misc_depth(m.x);
     uint32_t lseed = m.y;
@@ -196,8 +197,11 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         }
     }
 
-    const float3 add = s.radiance * throughput;  // raygen.cu:60 (radiance without NEE is 0 here)
-    ra.x += add.x; ra.y += add.y; ra.z += add.z;
+    // raygen.cu:60: sampleRadiance += radiance * throughput.  The scattering materials return radiance 0
+    // (NEE arrives through the shadow stage), so the sum only changes when the product is not +-0 —
+    // i.e. when throughput is inf/NaN; x + (+-0) == x for every x the sum can hold (it is never -0).
+    const float3 add = s.radiance * throughput;
+    const bool touch_rad = !(add.x == 0.0f && add.y == 0.0f && add.z == 0.0f);
     uint32_t state = RTW_ST_ALIVE;
     float3 origin = f3(ro);
     float3 dir = direction;
@@ -223,7 +227,11 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         w.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, rd.w);
     }
     w.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
-    w.rad[slot] = ra;
+    if (touch_rad) {
+        float4 ra = w.rad[slot];
+        ra.x += add.x; ra.y += add.y; ra.z += add.z;
+        w.rad[slot] = ra;
+    }
     w.misc[slot] = make_uint2(misc_pack(depth, state), lseed);
     return state != RTW_ST_ALIVE;
 }
