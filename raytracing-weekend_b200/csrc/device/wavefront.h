@@ -24,12 +24,10 @@ RTW_HD uint32_t misc_pack(uint32_t depth, uint32_t state) { return (depth & 0xff
 // ---- stage 0: flush a finished path, report whether the slot is free -------
 // removeNaNs + accumulation, raygen/raygen.cu:17-24,141.  On the device the add
 // is an atomic (several slots may hold samples of one pixel).
-RTW_HD bool logic_flush(const DWave& w, uint32_t slot) {
-    const uint2 m = w.misc[slot];
+RTW_HD bool logic_flush(const DWave& w, uint32_t slot, uint2 m, float4 ra) {
     const uint32_t st = misc_state(m.x);
     if (st == RTW_ST_ALIVE) return false;
     if (st == RTW_ST_DEAD) {
-        float4 ra = w.rad[slot];
         if (!(ra.x == ra.x)) ra.x = 0.0f;
         if (!(ra.y == ra.y)) ra.y = 0.0f;
         if (!(ra.z == ra.z)) ra.z = 0.0f;
@@ -47,11 +45,17 @@ RTW_HD bool logic_flush(const DWave& w, uint32_t slot) {
     return true;
 }
 
+RTW_HD bool logic_flush(const DWave& w, uint32_t slot) { return logic_flush(w, slot, w.misc[slot], w.rad[slot]); }
+
 // ---- stage 0b: start sample `ordinal` in a free slot -----------------------
 // raygen.cu:129-135 (seed, jitter), shaders/camera.cu:11-19 (camera ray, Q3),
 // raygen.cu:89-95 (color(): thePrd.seed = S4, gatherTime from the local seed, Q4),
 // raygen.cu:30,48 (rayColor(): local seed copy, first ray time).
-RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsigned long long ordinal) {
+struct NewPath {
+    float4 ray_o, ray_d, thr, rad;
+    uint2 misc;
+};
+RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long ordinal) {
     const unsigned long long npix = (unsigned long long)w.Nx * (unsigned long long)w.Ny;
     const uint32_t pixel = (uint32_t)(ordinal % npix);
     const uint32_t ki = (uint32_t)(ordinal / npix);
@@ -68,12 +72,24 @@ RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsig
     const float gather = sc.cam_time0 + rnd(seed) * (sc.cam_time1 - sc.cam_time0);
     uint32_t lseed = s4;
     const float ray_time = rnd(lseed);
-    w.ray_o[slot] = make_float4(origin.x, origin.y, origin.z, ray_time);
-    w.ray_d[slot] = make_float4(direction.x, direction.y, direction.z, gather);
-    w.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
-    w.rad[slot] = make_float4(0.f, 0.f, 0.f, u2f(pixel));
+    NewPath np;
+    np.ray_o = make_float4(origin.x, origin.y, origin.z, ray_time);
+    np.ray_d = make_float4(direction.x, direction.y, direction.z, gather);
+    np.thr = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
+    np.rad = make_float4(0.f, 0.f, 0.f, u2f(pixel));
     // `while (depth < maxRayDepth)` (raygen.cu:36): with a depth limit of 0 no ray is traced
-    w.misc[slot] = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
+    np.misc = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
+    return np;
+}
+RTW_HD void store_path(const DWave& w, uint32_t slot, const NewPath& np) {
+    w.ray_o[slot] = np.ray_o;
+    w.ray_d[slot] = np.ray_d;
+    w.thr[slot] = np.thr;
+    w.rad[slot] = np.rad;
+    w.misc[slot] = np.misc;
+}
+RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsigned long long ordinal) {
+    store_path(w, slot, make_path(sc, w, ordinal));
 }
 
 // ---- stage 1: closest-hit traversal + material classification --------------

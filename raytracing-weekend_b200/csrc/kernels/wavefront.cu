@@ -54,11 +54,20 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
     const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const uint32_t slot = q[i];
-        logic_flush(w, slot);
+        // the old path's state is requested first, the new path (tea<64>: ~1000 integer instructions,
+        // no memory) is computed while those loads are in flight, then flush, then store
+        const uint2 m = w.misc[slot];
+        const float4 ra = w.rad[slot];
         // queue position i takes sample ordinal next + i: no atomic (k_advance moves `next` on by n
         // after this kernel)
         const unsigned long long ordinal = next + (unsigned long long)i;
-        if (ordinal < w.total) generate_path(sc, w, slot, ordinal);
+        if (ordinal < w.total) {
+            const NewPath np = make_path(sc, w, ordinal);
+            logic_flush(w, slot, m, ra);
+            store_path(w, slot, np);
+        } else {
+            logic_flush(w, slot, m, ra);
+        }
     }
 }
 
