@@ -164,6 +164,11 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly ONE JSON line: everything else that libraries write to fd 1 (NCCL's version
+    # banner, extension build chatter) is sent to stderr; the line itself goes to the saved descriptor
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -179,6 +184,8 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL prints its version banner on stdout; stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     spp = args.spp
     # rank g renders samples k = g (mod world): counts differ by at most one
@@ -336,7 +343,8 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = cpu_sample(rtw, 15.0)
             line["cpu_baseline"] = cb
-        print(json.dumps(line), flush=True)
+        json_out.write(json.dumps(line) + "\n")
+        json_out.flush()
     d.destroy()
     if world > 1:
         dist.destroy_process_group()

@@ -1,0 +1,26 @@
+"""profiles/sass/: per-kernel SASS listings of librtw.so (cuobjdump -sass), encodings stripped.
+Usage: python tools/sass_split.py   (after `make -C raytracing-weekend_b200`)"""
+import os, re, subprocess
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+txt = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "raytracing-weekend_b200", "librtw.so")],
+                     capture_output=True, text=True, check=True).stdout
+out = os.path.join(ROOT, "profiles", "sass")
+os.makedirs(out, exist_ok=True)
+keep = {"k_traverse_flat", "k_shadow_flat", "k_traverse", "k_shadow", "k_shade_all", "k_regen", "k_advance", "k_karras",
+        "k_refit", "k_sort_scatter", "k_morton", "k_prim_aabb", "k_tonemap", "k_trace"}
+index = []
+for p in re.split(r"\n\s*Function : ", txt)[1:]:
+    name = p.split("\n", 1)[0].strip()
+    m = re.search(r"\d+(k_[a-z_]+)E", name)
+    short = m.group(1) if m else name[:40]
+    body = re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/", "", p)
+    body = "\n".join(l.rstrip() for l in body.split("\n") if l.strip())
+    index.append((short, len(re.findall(r"/\*[0-9a-f]{4,5}\*/", body))))
+    if short in keep:
+        open(os.path.join(out, short + ".sass"), "w").write("Function : " + body + "\n")
+with open(os.path.join(out, "INDEX.md"), "w") as f:
+    f.write("# SASS listings (cuobjdump -sass librtw.so, sm_100a, nvcc 12.9, -O3 -lineinfo -fmad=false)\n\n"
+            "Instruction counts per kernel; full text for the hot kernels beside this file (encodings stripped).\n"
+            "No tcgen05 / UTMA instructions are expected: the path has no dense contraction (BASELINE.json north_star).\n\n"
+            "| kernel | SASS instructions |\n|---|---|\n" + "\n".join("| %s | %d |" % x for x in index) + "\n")
+print(index)
