@@ -33,10 +33,10 @@ RTW_HD bool logic_flush(const DWave& w, uint32_t slot, uint2 m, float4 ra) {
         if (!(ra.z == ra.z)) ra.z = 0.0f;
         float* a = reinterpret_cast<float*>(w.accum + f2u(ra.w));
 #if defined(__CUDA_ARCH__)
-        atomicAdd(a + 0, ra.x);
-        atomicAdd(a + 1, ra.y);
-        atomicAdd(a + 2, ra.z);
-        atomicAdd(a + 3, 1.0f);
+        // one 16-byte vector reduction (sm_90+) instead of four scalar ones: the four lanes of the
+        // vector are independent fp32 adds, so the sums are the same bits
+        atomicAdd(w.accum + f2u(ra.w), make_float4(ra.x, ra.y, ra.z, 1.0f));
+        (void)a;
 #else
         a[0] += ra.x; a[1] += ra.y; a[2] += ra.z; a[3] += 1.0f;
 #endif
