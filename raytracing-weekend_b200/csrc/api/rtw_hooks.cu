@@ -96,11 +96,6 @@ extern "C" int rtw_camera_rays(rtw_ctx* c, int Nx, int Ny, int sample, rtw_ray* 
     const int npix = Nx * Ny;
     Tmp t;
     DWave w{};
-    RTW_CUDA(c, dalloc(t.pool, &w.ray_o, npix));
-    RTW_CUDA(c, dalloc(t.pool, &w.ray_d, npix));
-    RTW_CUDA(c, dalloc(t.pool, &w.thr, npix));
-    RTW_CUDA(c, dalloc(t.pool, &w.rad, npix));
-    RTW_CUDA(c, dalloc(t.pool, &w.misc, npix));
     rtw_ray* d_rays = nullptr;
     RTW_CUDA(c, dalloc(t.pool, &d_rays, npix));
     w.P = npix;

@@ -116,13 +116,27 @@ struct DScene {
 #define RTW_C_WORK_SHADOW  17              // next shadow-queue entry to fetch
 #define RTW_C_WORDS      20
 
+// Per-slot state is read and written through queue indices (a warp of the shading kernels holds
+// 32 arbitrary slots), so the records that are always used together are laid out as ONE 32-byte
+// sector each: a slot costs exactly the bytes it uses, whatever its neighbours do, and a record
+// moves with one 256-bit access (LDG.E.ENL2.256 / STG.E.ENL2.256).
+struct __align__(32) RayRec {
+    float4 o;           // origin.xyz, ray time   (o.w == RTW_RAY_NONE bits: the slot holds no live ray)
+    float4 d;           // direction.xyz, gather time
+};
+struct __align__(32) PathRec {
+    float4 thr;         // throughput.xyz, path seed bits
+    uint2 misc;         // (depth | state << 8, ray-time seed)
+    uint2 spare;        // written as zero so that a store covers the whole sector
+};
+#define RTW_RAY_NONE   0xffffffffu   // RayRec.o.w of a slot without a live ray (a ray time is a number in [0, 1))
+#define RTW_PIXEL_NONE 0xffffffffu   // rad.w of a slot that holds nothing to flush
+
 struct DWave {
-    float4* ray_o;      // origin.xyz, ray time
-    float4* ray_d;      // direction.xyz, gather time
-    uint2*  hit;        // (t bits, leaf index or RTW_REF_NONE)
-    float4* thr;        // throughput.xyz, path seed bits
-    float4* rad;        // radiance sum .xyz, pixel index bits
-    uint2*  misc;       // (depth | state << 8, ray-time seed)
+    RayRec*  ray;       // current ray of the slot
+    PathRec* st;        // throughput, seeds, depth
+    uint2*  hit;        // (t bits, leaf index or RTW_REF_NONE): written by the traversal in slot order
+    float4* rad;        // radiance sum .xyz, pixel index bits (touched only when light is added)
     uint32_t* queue;    // RTW_Q_SLOTS * P slot indices
     float4* sh_o;       // shadow queue: origin.xyz, tmax
     float4* sh_d;       //               direction.xyz, slot bits

@@ -21,39 +21,46 @@ RTW_HD uint32_t misc_state(uint32_t m) { return (m >> 8) & 3u; }
 RTW_HD uint32_t misc_depth(uint32_t m) { return m & 0xffu; }
 RTW_HD uint32_t misc_pack(uint32_t depth, uint32_t state) { return (depth & 0xffu) | (state << 8); }
 
-// ---- stage 0: flush a finished path, report whether the slot is free -------
+// ---- stage 0: flush a finished path ---------------------------------------
 // removeNaNs + accumulation, raygen/raygen.cu:17-24,141.  On the device the add
-// is an atomic (several slots may hold samples of one pixel).
-RTW_HD bool logic_flush(const DWave& w, uint32_t slot, uint2 m, float4 ra) {
-    const uint32_t st = misc_state(m.x);
-    if (st == RTW_ST_ALIVE) return false;
-    if (st == RTW_ST_DEAD) {
-        if (!(ra.x == ra.x)) ra.x = 0.0f;
-        if (!(ra.y == ra.y)) ra.y = 0.0f;
-        if (!(ra.z == ra.z)) ra.z = 0.0f;
-        float* a = reinterpret_cast<float*>(w.accum + f2u(ra.w));
+// is an atomic (several slots may hold samples of one pixel).  `ra` is the slot's
+// radiance record; a slot that never held a path carries RTW_PIXEL_NONE.
+RTW_HD void logic_flush(const DWave& w, float4 ra) {
+    if (f2u(ra.w) == RTW_PIXEL_NONE) return;
+    if (!(ra.x == ra.x)) ra.x = 0.0f;
+    if (!(ra.y == ra.y)) ra.y = 0.0f;
+    if (!(ra.z == ra.z)) ra.z = 0.0f;
 #if defined(__CUDA_ARCH__)
-        // one 16-byte vector reduction (sm_90+) instead of four scalar ones: the four lanes of the
-        // vector are independent fp32 adds, so the sums are the same bits
-        atomicAdd(w.accum + f2u(ra.w), make_float4(ra.x, ra.y, ra.z, 1.0f));
-        (void)a;
+    // one 16-byte vector reduction (sm_90+) instead of four scalar ones: the four lanes of the
+    // vector are independent fp32 adds, so the sums are the same bits
+    atomicAdd(w.accum + f2u(ra.w), make_float4(ra.x, ra.y, ra.z, 1.0f));
 #else
-        a[0] += ra.x; a[1] += ra.y; a[2] += ra.z; a[3] += 1.0f;
+    float* a = reinterpret_cast<float*>(w.accum + f2u(ra.w));
+    a[0] += ra.x; a[1] += ra.y; a[2] += ra.z; a[3] += 1.0f;
 #endif
-        w.misc[slot] = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
-    }
-    return true;
 }
-
-RTW_HD bool logic_flush(const DWave& w, uint32_t slot) { return logic_flush(w, slot, w.misc[slot], w.rad[slot]); }
+// A slot that is not refilled (no sample left to start): nothing to trace, nothing to flush again.
+RTW_HD void retire_slot(const DWave& w, uint32_t slot) {
+    RayRec none;
+    none.o = make_float4(0.f, 0.f, 0.f, u2f(RTW_RAY_NONE));
+    none.d = make_float4(0.f, 0.f, 0.f, 0.f);
+    w.ray[slot] = none;
+    PathRec st;
+    st.thr = make_float4(0.f, 0.f, 0.f, 0.f);
+    st.misc = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
+    st.spare = make_uint2(0u, 0u);
+    w.st[slot] = st;
+    w.rad[slot] = make_float4(0.f, 0.f, 0.f, u2f(RTW_PIXEL_NONE));
+}
 
 // ---- stage 0b: start sample `ordinal` in a free slot -----------------------
 // raygen.cu:129-135 (seed, jitter), shaders/camera.cu:11-19 (camera ray, Q3),
 // raygen.cu:89-95 (color(): thePrd.seed = S4, gatherTime from the local seed, Q4),
 // raygen.cu:30,48 (rayColor(): local seed copy, first ray time).
 struct NewPath {
-    float4 ray_o, ray_d, thr, rad;
-    uint2 misc;
+    RayRec ray;
+    PathRec st;
+    float4 rad;
 };
 RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long ordinal) {
     const unsigned long long npix = (unsigned long long)w.Nx * (unsigned long long)w.Ny;
@@ -73,20 +80,19 @@ RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long or
     uint32_t lseed = s4;
     const float ray_time = rnd(lseed);
     NewPath np;
-    np.ray_o = make_float4(origin.x, origin.y, origin.z, ray_time);
-    np.ray_d = make_float4(direction.x, direction.y, direction.z, gather);
-    np.thr = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
+    np.ray.o = make_float4(origin.x, origin.y, origin.z, ray_time);
+    np.ray.d = make_float4(direction.x, direction.y, direction.z, gather);
+    np.st.thr = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
+    np.st.spare = make_uint2(0u, 0u);
     np.rad = make_float4(0.f, 0.f, 0.f, u2f(pixel));
     // `while (depth < maxRayDepth)` (raygen.cu:36): with a depth limit of 0 no ray is traced
-    np.misc = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
+    np.st.misc = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
     return np;
 }
 RTW_HD void store_path(const DWave& w, uint32_t slot, const NewPath& np) {
-    w.ray_o[slot] = np.ray_o;
-    w.ray_d[slot] = np.ray_d;
-    w.thr[slot] = np.thr;
+    w.ray[slot] = np.ray;
+    w.st[slot] = np.st;
     w.rad[slot] = np.rad;
-    w.misc[slot] = np.misc;
 }
 RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsigned long long ordinal) {
     store_path(w, slot, make_path(sc, w, ordinal));
@@ -97,10 +103,9 @@ RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsig
 // shading queue class of the slot, or -1 if the slot holds no live path.
 template <class Mem>
 RTW_HD int traverse_thread(const DScene& sc, const float4* top, const DWave& w, uint32_t slot) {
-    const uint2 m = w.misc[slot];
-    if (misc_state(m.x) != RTW_ST_ALIVE) return -1;
-    const float4 ro = w.ray_o[slot];
-    const float4 rd = w.ray_d[slot];
+    const RayRec ray = w.ray[slot];
+    const float4 ro = ray.o, rd = ray.d;
+    if (f2u(ro.w) == RTW_RAY_NONE) return -1;
     RayW r;
     r.o = f3(ro);
     r.d = f3(rd);
@@ -108,7 +113,7 @@ RTW_HD int traverse_thread(const DScene& sc, const float4* top, const DWave& w, 
     r.tmax = 1.e27f;  // shaders/appconfig.h:3
     r.time = ro.w;
     r.gather = rd.w;
-    r.seed = sc.has_media ? f2u(w.thr[slot].w) : 0u;
+    r.seed = sc.has_media ? f2u(w.st[slot].thr.w) : 0u;
     float t;
     uint32_t leaf;
     const bool found = traverse_closest<Mem, false>(sc, top, r, t, leaf, nullptr);
@@ -138,13 +143,14 @@ struct ShadowOut {
 template <int kClass, class Mem>
 RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh) {
     sh.emit = false;
-    const float4 ro = w.ray_o[slot];
-    const float4 rd = w.ray_d[slot];
+    const RayRec ray = w.ray[slot];
+    const PathRec st = w.st[slot];
     const uint2 hit = w.hit[slot];
-    const float4 th = w.thr[slot];
+    const float4 ro = ray.o, rd = ray.d;
+    const float4 th = st.thr;
     float4 ra = make_float4(0.f, 0.f, 0.f, 0.f);
     if (kClass == RTW_Q_TERMINAL) ra = w.rad[slot];   // the scattering classes touch the sum only in the rare case below
-    const uint2 m = w.misc[slot];
+    const uint2 m = st.misc;
     uint32_t depth = misc_depth(m.x);
     uint32_t lseed = m.y;
     uint32_t seed = f2u(th.w);
@@ -171,8 +177,7 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         }
         const float3 add = radiance * throughput;  // raygen.cu:60
         ra.x += add.x; ra.y += add.y; ra.z += add.z;
-        w.rad[slot] = ra;
-        w.misc[slot] = make_uint2(misc_pack(depth, RTW_ST_DEAD), lseed);
+        w.rad[slot] = ra;   // the path record is not needed again: the slot goes to the regen queue
         return true;
     }
 
@@ -239,16 +244,21 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
     }
     if (state == RTW_ST_ALIVE) {
         const float ray_time = rnd(lseed);  // raygen.cu:48
-        w.ray_o[slot] = make_float4(origin.x, origin.y, origin.z, ray_time);
-        w.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, rd.w);
+        RayRec next;
+        next.o = make_float4(origin.x, origin.y, origin.z, ray_time);
+        next.d = make_float4(dir.x, dir.y, dir.z, rd.w);
+        w.ray[slot] = next;
+        PathRec ns;
+        ns.thr = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
+        ns.misc = make_uint2(misc_pack(depth, state), lseed);
+        ns.spare = make_uint2(0u, 0u);
+        w.st[slot] = ns;
     }
-    w.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
     if (touch_rad) {
         float4 ra = w.rad[slot];
         ra.x += add.x; ra.y += add.y; ra.z += add.z;
         w.rad[slot] = ra;
     }
-    w.misc[slot] = make_uint2(misc_pack(depth, state), lseed);
     return state != RTW_ST_ALIVE;
 }
 
@@ -266,7 +276,7 @@ RTW_HD void shadow_thread(const DScene& sc, const float4* top, const DWave& w, u
     r.tmin = 500 * 1.0e-7f;
     r.tmax = so.w;
     r.time = 0.0f;
-    r.gather = sc.has_motion ? w.ray_d[slot].w : 0.f;
+    r.gather = sc.has_motion ? w.ray[slot].d.w : 0.f;
     r.seed = f2u(c.w);
     if (!traverse_any<Mem, false>(sc, top, r, nullptr)) {
         float4 ra = w.rad[slot];

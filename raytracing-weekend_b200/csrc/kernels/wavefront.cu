@@ -56,17 +56,17 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
         const uint32_t slot = q[i];
         // the old path's state is requested first, the new path (tea<64>: ~1000 integer instructions,
         // no memory) is computed while those loads are in flight, then flush, then store
-        const uint2 m = w.misc[slot];
         const float4 ra = w.rad[slot];
         // queue position i takes sample ordinal next + i: no atomic (k_advance moves `next` on by n
         // after this kernel)
         const unsigned long long ordinal = next + (unsigned long long)i;
         if (ordinal < w.total) {
             const NewPath np = make_path(sc, w, ordinal);
-            logic_flush(w, slot, m, ra);
+            logic_flush(w, ra);
             store_path(w, slot, np);
         } else {
-            logic_flush(w, slot, m, ra);
+            logic_flush(w, ra);
+            retire_slot(w, slot);
         }
     }
 }
@@ -109,17 +109,16 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     __device__ uint32_t count() const { return (uint32_t)w.P; }
     __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_CLOSEST; }
     __device__ bool load(uint32_t slot, RayW& r) const {
-        const uint2 m = w.misc[slot];
-        if (misc_state(m.x) != RTW_ST_ALIVE) return false;
-        const float4 ro = w.ray_o[slot];
-        const float4 rd = w.ray_d[slot];
+        const RayRec ray = w.ray[slot];
+        const float4 ro = ray.o, rd = ray.d;
+        if (f2u(ro.w) == RTW_RAY_NONE) return false;
         r.o = f3(ro);
         r.d = f3(rd);
         r.tmin = 1e-6f;
         r.tmax = 1.e27f;   // shaders/appconfig.h:3
         r.time = ro.w;
         r.gather = rd.w;
-        r.seed = sc.has_media ? f2u(w.thr[slot].w) : 0u;
+        r.seed = sc.has_media ? f2u(w.st[slot].thr.w) : 0u;
         return true;
     }
     // returns the shading class of the finished slot
@@ -149,7 +148,7 @@ struct ShadowJob {       // stage 3: the NEE rays (closehit.cu:16-42,97-113): tm
         r.tmin = 500 * 1.0e-7f;
         r.tmax = so.w;
         r.time = 0.0f;
-        r.gather = sc.has_motion ? w.ray_d[f2u(sd.w)].w : 0.f;
+        r.gather = sc.has_motion ? w.ray[f2u(sd.w)].d.w : 0.f;
         r.seed = f2u(w.sh_c[i].w);
         return true;
     }
@@ -385,7 +384,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave 
 __global__ void __launch_bounds__(kBlock) k_wave_init(const DWave w) {
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < (uint32_t)w.P; slot += stride) {
-        w.misc[slot] = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
+        retire_slot(w, slot);
         w.queue[(size_t)RTW_Q_REGEN * w.P + slot] = slot;   // every slot is free: the first k_regen fills the pool
     }
     if (blockIdx.x == 0 && threadIdx.x < RTW_C_WORDS)
@@ -458,8 +457,8 @@ __global__ void __launch_bounds__(kBlock) k_camera_rays(const DScene sc, const D
     const uint32_t npix = (uint32_t)w.Nx * (uint32_t)w.Ny;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npix) return;
-    generate_path(sc, w, i, (unsigned long long)i);
-    const float4 ro = w.ray_o[i], rd = w.ray_d[i], th = w.thr[i];
+    const NewPath np = make_path(sc, w, (unsigned long long)i);
+    const float4 ro = np.ray.o, rd = np.ray.d, th = np.st.thr;
     rtw_ray r;
     r.origin[0] = ro.x; r.origin[1] = ro.y; r.origin[2] = ro.z;
     r.dir[0] = rd.x; r.dir[1] = rd.y; r.dir[2] = rd.z;

@@ -283,12 +283,14 @@ extern "C" void emu_trace(const Emu* e, const rtw_ray* rays, int n, rtw_hit* hit
 extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sample_stride, int sample_count,
                           int max_depth, int P, float* accum, unsigned long long* stats /* rays, shadow rays, iterations */) {
     const DScene& sc = e->sc;
-    std::vector<float4> ray_o(P), ray_d(P), thr(P), rad(P), sh_o(P), sh_d(P), sh_c(P);
-    std::vector<uint2> hit(P), misc(P, make_uint2(0, 0));
+    std::vector<RayRec> ray(P);
+    std::vector<PathRec> st(P);
+    std::vector<float4> rad(P), sh_o(P), sh_d(P), sh_c(P);
+    std::vector<uint2> hit(P);
     std::vector<uint32_t> queue((size_t)RTW_Q_SLOTS * P), counters(RTW_C_WORDS, 0);
     DWave w{};
-    w.ray_o = ray_o.data(); w.ray_d = ray_d.data(); w.hit = hit.data(); w.thr = thr.data(); w.rad = rad.data();
-    w.misc = misc.data(); w.queue = queue.data(); w.sh_o = sh_o.data(); w.sh_d = sh_d.data(); w.sh_c = sh_c.data();
+    w.ray = ray.data(); w.st = st.data(); w.hit = hit.data(); w.rad = rad.data();
+    w.queue = queue.data(); w.sh_o = sh_o.data(); w.sh_d = sh_d.data(); w.sh_c = sh_c.data();
     w.counters = counters.data(); w.accum = reinterpret_cast<float4*>(accum);
     w.P = P; w.Nx = Nx; w.Ny = Ny; w.max_depth = max_depth;
     w.sample_first = sample_first; w.sample_stride = sample_stride;
@@ -300,14 +302,18 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
         return 0;
     }
     uint32_t* regen = queue.data() + (size_t)RTW_Q_REGEN * P;
-    for (int slot = 0; slot < P; slot++) regen[slot] = (uint32_t)slot;   // k_wave_init
+    for (int slot = 0; slot < P; slot++) {   // k_wave_init
+        retire_slot(w, slot);
+        regen[slot] = (uint32_t)slot;
+    }
     counters[RTW_C_QUEUE0 + RTW_Q_REGEN] = (uint32_t)P;
     for (;;) {
         for (uint32_t i = 0; i < counters[RTW_C_QUEUE0 + RTW_Q_REGEN]; i++) {  // k_regen
             const uint32_t slot = regen[i];
-            logic_flush(w, slot);
+            logic_flush(w, w.rad[slot]);
             const unsigned long long ord = next++;
             if (ord < w.total) generate_path(sc, w, slot, ord);
+            else retire_slot(w, slot);
         }
         for (int c = 0; c < 8; c++) counters[c] = 0;
         iters++;
@@ -349,18 +355,15 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
 
 extern "C" void emu_camera_rays(const Emu* e, int Nx, int Ny, int sample, rtw_ray* out) {
     const int npix = Nx * Ny;
-    std::vector<float4> ray_o(npix), ray_d(npix), thr(npix), rad(npix);
-    std::vector<uint2> misc(npix);
     DWave w{};
-    w.ray_o = ray_o.data(); w.ray_d = ray_d.data(); w.thr = thr.data(); w.rad = rad.data(); w.misc = misc.data();
     w.P = npix; w.Nx = Nx; w.Ny = Ny; w.sample_first = sample; w.sample_stride = 0; w.total = npix;
     for (int i = 0; i < npix; i++) {
-        generate_path(e->sc, w, i, (unsigned long long)i);
+        const NewPath np = make_path(e->sc, w, (unsigned long long)i);
         rtw_ray& r = out[i];
-        r.origin[0] = ray_o[i].x; r.origin[1] = ray_o[i].y; r.origin[2] = ray_o[i].z;
-        r.dir[0] = ray_d[i].x; r.dir[1] = ray_d[i].y; r.dir[2] = ray_d[i].z;
-        r.tmin = 1e-6f; r.tmax = 1.e27f; r.time = ray_o[i].w; r.gather_time = ray_d[i].w;
-        r.seed = f2u(thr[i].w); r.pad = 0;
+        r.origin[0] = np.ray.o.x; r.origin[1] = np.ray.o.y; r.origin[2] = np.ray.o.z;
+        r.dir[0] = np.ray.d.x; r.dir[1] = np.ray.d.y; r.dir[2] = np.ray.d.z;
+        r.tmin = 1e-6f; r.tmax = 1.e27f; r.time = np.ray.o.w; r.gather_time = np.ray.d.w;
+        r.seed = f2u(np.st.thr.w); r.pad = 0;
     }
 }
 
