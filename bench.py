@@ -294,15 +294,15 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD if spp == SPP else WORKLOAD.replace("1024 spp", "%d spp (override)" % spp),
                            "parallelism": "sample-sharded x%d, one NCCL reduce per frame" % world,
-                           "l2_policy": "inputs larger than L2: the wavefront pool (2^21 path slots x 152 B state + queues = 319 MB) "
+                           "l2_policy": "inputs larger than L2: the wavefront pool (2^21 path slots x 160 B state + queues = 336 MB) "
                                         "streams through HBM every iteration, no flush between steps",
                            "wall_ms_per_step": wall / args.steps * 1e3},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},
                 "gpu_launches": int(tot[2].item()), "clocks": clk.summary()}
         # ---- roofline of the dominant kernel: k_traverse (closest-hit traversal) ----
-        # HBM-visible ALGORITHMIC bytes per ray: misc 8 + ray_o 16 + ray_d 16 read,
-        # hit 8 + queue entry 4 written = 52 B.  The BVH nodes / primitive records of SURVEY.md §8d
+        # HBM-visible ALGORITHMIC bytes per ray: the 32-byte ray record read,
+        # hit 8 + queue entry 4 written = 44 B.  The BVH nodes / primitive records of SURVEY.md §8d
         # (64 B x nodes + 32 B x primitives, +48 B per transformed run) are served by L1 / shared memory
         # for this scene; they are reported beside it from the ORACLE's visit counters on its mirror
         # of the hierarchy, not from the GPU.
@@ -312,7 +312,7 @@ def main():
         rc = max(c["rays_closest"], 1)
         onchip_per_ray = (64.0 * c["nodes_closest"] + 32.0 * (c["prims_closest"] - c["prims_xf_closest"]) +
                           80.0 * c["prims_xf_closest"]) / rc
-        hbm_per_ray = 52.0
+        hbm_per_ray = 44.0
         iters = max(agg["iters"], 1)
         trav_s = agg["trav_ms"] * 1e-3
         achieved = agg["rays"] * hbm_per_ray / max(trav_s, 1e-9) / 1e9
@@ -323,8 +323,12 @@ def main():
         # per-stage picture of one wavefront iteration (HBM-visible algorithmic bytes per unit)
         n_paths = float(NX * NY * spp) * args.steps / world
         stages = {}
-        for name, ms, units, bpu in (("k_traverse", agg["trav_ms"], agg["rays"], 52.0),
-                                     ("k_shade*", agg["shade_ms"], agg["rays"], 156.0 + 48.0 * agg["shrays"] / max(agg["rays"], 1)),
+        fin = n_paths / max(agg["rays"], 1)          # share of shaded vertices that end their path
+        # k_shade_all per vertex: queue entry 4 + ray 32 + path 32 + hit 8 read; a continuing path writes ray 32 +
+        # path 32, an ending one its radiance record (16 R + 16 W) and a regen entry 4; + 48 per NEE ray emitted
+        shade_bpu = 76.0 + 64.0 * (1.0 - fin) + 36.0 * fin + 48.0 * agg["shrays"] / max(agg["rays"], 1)
+        for name, ms, units, bpu in (("k_traverse", agg["trav_ms"], agg["rays"], hbm_per_ray),
+                                     ("k_shade*", agg["shade_ms"], agg["rays"], shade_bpu),
                                      ("k_shadow", agg["shadow_ms"], agg["shrays"], 72.0),
                                      ("k_regen", agg["logic_ms"], n_paths, 116.0)):
             gbs = units * bpu / max(ms * 1e-3, 1e-9) / 1e9

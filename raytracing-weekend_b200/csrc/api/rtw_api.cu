@@ -107,6 +107,9 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
         else if (name[5] == 'n') c->opt_step_nodes = (int)value;
         else c->opt_step_prims = (int)value;
         c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;
+    } else if (!strcmp(name, "small")) {
+        if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "small out of range [-1, 1]");
+        c->opt_small = (int)value;
     } else if (!strcmp(name, "walker")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "walker out of range [-1, 1]");
         c->opt_walker = (int)value;
@@ -383,6 +386,24 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // lose ~10 % on the 520-528 primitive scenes, where rays finish within a few steps of each other and
     // the finish-order queue pushes cost the shading kernels their slot-order coalescing.
     c->cfg.walker = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 1024);
+    // Small scenes (one leaf range, <= RTW_SMALL_MAX leaves and transforms): the leaf records go to
+    // the traversal kernels by value.
+    c->cfg.small = nullptr;
+    if (c->opt_small != 0 && !(c->opt_walker == 1) && (sc.root & RTW_REF_LEAF) && n <= RTW_SMALL_MAX && c->n_xforms <= RTW_SMALL_MAX) {
+        SmallScene& ss = c->small;
+        memset(&ss, 0, sizeof(ss));
+        ss.n = n;
+        float4 xf[6 * RTW_SMALL_MAX];
+        RTW_CUDA(c, cudaMemcpyAsync(ss.prim, b.prims_packed, sizeof(float4) * 2 * n, cudaMemcpyDeviceToHost, c->stream));
+        RTW_CUDA(c, cudaMemcpyAsync(ss.ext, b.prim_ext, sizeof(float2) * n, cudaMemcpyDeviceToHost, c->stream));
+        RTW_CUDA(c, cudaMemcpyAsync(ss.prim_id, b.leaf_prim, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+        if (c->n_xforms > 0)
+            RTW_CUDA(c, cudaMemcpyAsync(xf, sc.xforms, sizeof(float4) * 6 * c->n_xforms, cudaMemcpyDeviceToHost, c->stream));
+        RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int j = 0; j < c->n_xforms; j++)
+            for (int k = 0; k < 3; k++) ss.w2o[3 * j + k] = xf[6 * j + k];
+        c->cfg.small = &c->small;
+    }
     RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
     c->cfg.class_mask = c->class_mask;
     c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;

@@ -21,6 +21,7 @@ struct rtw_ctx {
     rtw::BuildBuffers build{};
     rtw::DScene scene{};
     rtw::LaunchCfg cfg{};
+    rtw::SmallScene small{};          // filled by rtw_build_accel when the scene is one leaf range of <= RTW_SMALL_MAX
     int n_internal = 0;
     int leaf_size = 1;
     float scene_min[3] = {0, 0, 0}, scene_max[3] = {0, 0, 0};
@@ -44,6 +45,7 @@ struct rtw_ctx {
     long long opt_pool_paths = 1 << 21;
     int opt_top_nodes = 1024;
     int opt_leaf_size = 0;
+    int opt_small = -1;              // -1 = auto, 0 = never, 1 = whenever the scene qualifies
     int opt_walker = -1;             // -1 = auto (rtw_build_accel), 0 = flat kernels, 1 = persistent walkers
     int opt_step_nodes = 16, opt_step_prims = 8, opt_min_active = 22;   // measured best on the Book-2 scene (tools/sweep_walk.sh)          // 0 = auto (rtw_build_accel), else 1..32
     int opt_profile = 0;

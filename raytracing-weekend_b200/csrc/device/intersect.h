@@ -78,6 +78,45 @@ RTW_HD bool hit_boundary_sphere(float3 direction, float3 origin, float3 center, 
     return false;
 }
 
+// Where the traversal reads a leaf from.  SrcScene: the packed arrays in global memory
+// (per-lane leaf index).  SrcSmall (traverse.h): the kernel-parameter copy of a scene of
+// <= RTW_SMALL_MAX leaves, indexed by a warp-uniform loop counter.
+template <class Mem>
+struct SrcScene {
+    const DScene& sc;
+    RTW_HD void prim(uint32_t leaf, float4& a, float4& b) const {
+        a = Mem::ld4(sc.prims + 2 * leaf);
+        b = Mem::ld4(sc.prims + 2 * leaf + 1);
+    }
+    RTW_HD void w2o(int xf, float4& r0, float4& r1, float4& r2) const {
+        const float4* m = sc.xforms + 6 * xf;
+        r0 = Mem::ld4(m); r1 = Mem::ld4(m + 1); r2 = Mem::ld4(m + 2);
+    }
+    RTW_HD float2 ext(uint32_t leaf) const {
+#if defined(__CUDA_ARCH__)
+        return __ldg(sc.prim_ext + leaf);
+#else
+        return sc.prim_ext[leaf];
+#endif
+    }
+    RTW_HD int prim_id(uint32_t leaf) const {
+#if defined(__CUDA_ARCH__)
+        return __ldg(sc.leaf_prim + leaf);
+#else
+        return sc.leaf_prim[leaf];
+#endif
+    }
+};
+struct SrcSmall {
+    const SmallScene& ss;
+    RTW_HD void prim(uint32_t leaf, float4& a, float4& b) const { a = ss.prim[2 * leaf]; b = ss.prim[2 * leaf + 1]; }
+    RTW_HD void w2o(int xf, float4& r0, float4& r1, float4& r2) const {
+        r0 = ss.w2o[3 * xf]; r1 = ss.w2o[3 * xf + 1]; r2 = ss.w2o[3 * xf + 2];
+    }
+    RTW_HD float2 ext(uint32_t leaf) const { return ss.ext[leaf]; }
+    RTW_HD int prim_id(uint32_t leaf) const { return ss.prim_id[leaf]; }
+};
+
 // The world ray carried through an instance transform, remembered between the
 // primitives of one traversal: consecutive leaves mostly share their instance (the six
 // faces of a box, the 1000 small spheres of scene 4), so the 3x4 product is done once
@@ -87,93 +126,48 @@ struct XfRay {
     float3 o, d;
 };
 
-// Object-space ray of the primitive (a, b, meta).
-template <class Mem>
-RTW_HD void object_ray(const DScene& sc, float4 a, float4 b, uint32_t meta, const RayW& r, XfRay& cache, float3& o,
-                       float3& d) {
-    const int type = meta_type(meta);
-    o = r.o;
-    d = r.d;
-    if (type == RTW_PRIM_MOVING_SPHERE) {
-        o = r.o - motion_translation(a, b, r.time);
-    } else {
-        const int xf = meta_xform(meta);
-        if (xf >= 0) {
-            if (xf != cache.xf) {
-                const float4* m = sc.xforms + 6 * xf;
-                float4 r0 = Mem::ld4(m), r1 = Mem::ld4(m + 1), r2 = Mem::ld4(m + 2);
-                cache.o = xform_point(r0, r1, r2, r.o);
-                cache.d = xform_vector(r0, r1, r2, r.d);
-                cache.xf = xf;
-            }
-            o = cache.o;
-            d = cache.d;
-        }
-    }
+// ---- the candidate tests, one per primitive kind, on an object-space ray ----
+// shaders/aarectx.cu:8-49 (aarecty, aarectz alike): plane distance from the normal axis
+// (on, dn), in-plane coordinates from the other two.
+RTW_HD bool rect_candidate(float4 a, float k, float on, float dn, float o1, float d1, float o2, float d2, float tmin,
+                           float tmax, float& t_out) {
+    // A path leaving a rect has its origin ON that plane about half of the time, so k - on is
+    // exactly 0 for one primitive per ray; 0 / dn would take the division's out-of-line slow path
+    // (zero numerator) on a few lanes in every iteration.  0 * (+-1) is the same value: +-0 with the
+    // quotient's sign, NaN when dn is 0 or NaN.
+    const float num = k - on;
+    float t;
+    if (num == 0.0f) t = num * ((dn > 0.0f || dn < 0.0f) ? copysignf(1.0f, dn) : NAN);
+    else t = num / dn;
+    const float pa = o1 + t * d1;
+    const float pb = o2 + t * d2;
+    if (t > tmax || t < tmin) return false;
+    if (pa < a.x || pa > a.y || pb < a.z || pb > a.w) return false;
+    if (!(t >= tmin && t <= tmax)) return false;  // rejects NaN
+    t_out = t;
+    return true;
 }
-
-// True (and the accepted distance) iff leaf `leaf` reports an intersection that
-// optixReportIntersection would accept for ray r.
-template <class Mem>
-RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, XfRay& cache, float& t_out) {
-    const float4 a = Mem::ld4(sc.prims + 2 * leaf);
-    const float4 b = Mem::ld4(sc.prims + 2 * leaf + 1);
-    const uint32_t meta = f2u(b.w);
-    const int type = meta_type(meta);
-    float3 o, d;
-    object_ray<Mem>(sc, a, b, meta, r, cache, o, d);
+// geometry/sphere.cu:48-120, geometry/movingSphere.cu:61-135 (centre c already resolved)
+RTW_HD bool sphere_candidate(float3 c, float radius, float3 o, float3 d, float tmin, float tmax, float& t_out) {
+    float3 oc = o - c;
+    float qa = dot(d, d);
+    float qb = dot(oc, d);
+    float qc = dot(oc, oc) - radius * radius;
+    float discriminant = qb * qb - qa * qc;
+    if (discriminant < 0.0f) return false;
+    float sq = sqrtf(discriminant);
+    float t = (-qb - sq) / qa;
+    if (t < tmax && t > tmin) { t_out = t; return true; }
+    t = (-qb + sq) / qa;
+    if (t < tmax && t > tmin) { t_out = t; return true; }
+    return false;
+}
+// geometry/volumeBox.cu:54-113, geometry/volumeSphere.cu:63-127; EPSILON is `constexpr int` == 0
+// in the reference (Q23); the free-flight draw is keyed by (ray seed, primitive id).
+RTW_HD bool medium_candidate(bool box, float4 a, float4 b, int prim, float3 o, float3 d, const RayW& r, float& t_out) {
     const float tmin = r.tmin, tmax = r.tmax;
-    if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
-        const float k = b.x;
-        // one instruction stream for the three axes (selects, no branches):
-        //   X: t from x, (pa, pb) = (y, z);  Y: t from y, (x, z);  Z: t from z, (x, y)
-        const bool ax = type == RTW_PRIM_RECT_X, az = type == RTW_PRIM_RECT_Z;
-        const float on = ax ? o.x : (az ? o.z : o.y), dn = ax ? d.x : (az ? d.z : d.y);
-        const float o1 = ax ? o.y : o.x, d1 = ax ? d.y : d.x;
-        const float o2 = az ? o.y : o.z, d2 = az ? d.y : d.z;
-        // A path leaving a rect has its origin ON that plane about half of the time, so k - on is
-        // exactly 0 for one primitive per ray; 0 / dn would take the division's out-of-line slow path
-        // (zero numerator) on a few lanes in every iteration.  0 * (+-1) is the same value: +-0 with the
-        // quotient's sign, NaN when dn is 0 or NaN.
-        const float num = k - on;
-        float t;
-        if (num == 0.0f) t = num * ((dn > 0.0f || dn < 0.0f) ? copysignf(1.0f, dn) : NAN);
-        else t = num / dn;
-        const float pa = o1 + t * d1;
-        const float pb = o2 + t * d2;
-        if (t > tmax || t < tmin) return false;
-        if (pa < a.x || pa > a.y || pb < a.z || pb > a.w) return false;
-        if (!(t >= tmin && t <= tmax)) return false;  // rejects NaN
-        t_out = t;
-        return true;
-    }
-    if (type == RTW_PRIM_SPHERE || type == RTW_PRIM_MOVING_SPHERE) {
-        float3 c = f3(a);
-        if (type == RTW_PRIM_MOVING_SPHERE) {
-#if defined(__CUDA_ARCH__)
-            float2 times = __ldg(sc.prim_ext + leaf);
-#else
-            float2 times = sc.prim_ext[leaf];
-#endif
-            c = moving_center(a, b, times, r.gather);
-        }
-        const float radius = a.w;
-        float3 oc = o - c;
-        float qa = dot(d, d);
-        float qb = dot(oc, d);
-        float qc = dot(oc, oc) - radius * radius;
-        float discriminant = qb * qb - qa * qc;
-        if (discriminant < 0.0f) return false;
-        float sq = sqrtf(discriminant);
-        float t = (-qb - sq) / qa;
-        if (t < tmax && t > tmin) { t_out = t; return true; }
-        t = (-qb + sq) / qa;
-        if (t < tmax && t > tmin) { t_out = t; return true; }
-        return false;
-    }
-    // constant media; EPSILON is `constexpr int` == 0 in the reference (Q23)
     float hitt1, hitt2, density;
-    if (type == RTW_PRIM_VOLUME_BOX) {
+    if (box) {
         density = a.w;
         float3 bmin = f3(a), bmax = f3(b);
         if (!hit_boundary_box(d, o, bmin, bmax, -RTW_FLT_MAX, RTW_FLT_MAX, hitt1)) return false;
@@ -188,18 +182,102 @@ RTW_HD bool prim_candidate(const DScene& sc, uint32_t leaf, const RayW& r, XfRay
     if (hitt2 > tmax) hitt2 = tmax;
     if (hitt1 >= hitt2) return false;
     if (hitt1 < 0.f) hitt1 = 0.f;
-#if defined(__CUDA_ARCH__)
-    const int prim = __ldg(sc.leaf_prim + leaf);
-#else
-    const int prim = sc.leaf_prim[leaf];
-#endif
     uint32_t st = medium_state(r.seed, (uint32_t)prim);
-    float u = (type == RTW_PRIM_VOLUME_BOX) ? randf(st) : rnd(st);  // volumeBox.cu:79 / volumeSphere.cu:93
+    float u = box ? randf(st) : rnd(st);  // volumeBox.cu:79 / volumeSphere.cu:93
     float hitDistance = -(1.f / density) * det_logf(u);
     float hitt = hitt1 + (hitDistance / length(d));
     if (!(hitt >= tmin && hitt <= tmax)) return false;
     t_out = hitt;
     return true;
+}
+
+// Object-space ray of the primitive (a, b, meta).
+template <class Src>
+RTW_HD void object_ray(const Src& src, float4 a, float4 b, uint32_t meta, const RayW& r, XfRay& cache, float3& o,
+                       float3& d) {
+    const int type = meta_type(meta);
+    o = r.o;
+    d = r.d;
+    if (type == RTW_PRIM_MOVING_SPHERE) {
+        o = r.o - motion_translation(a, b, r.time);
+    } else {
+        const int xf = meta_xform(meta);
+        if (xf >= 0) {
+            if (xf != cache.xf) {
+                float4 r0, r1, r2;
+                src.w2o(xf, r0, r1, r2);
+                cache.o = xform_point(r0, r1, r2, r.o);
+                cache.d = xform_vector(r0, r1, r2, r.d);
+                cache.xf = xf;
+            }
+            o = cache.o;
+            d = cache.d;
+        }
+    }
+}
+
+// True (and the accepted distance) iff leaf `leaf` reports an intersection that
+// optixReportIntersection would accept for ray r.  Lanes of a warp may hold different
+// leaves here: the three rect axes are one instruction stream (selects, no branches).
+template <class Src>
+RTW_HD bool prim_candidate(const Src& src, uint32_t leaf, const RayW& r, XfRay& cache, float& t_out) {
+    float4 a, b;
+    src.prim(leaf, a, b);
+    const uint32_t meta = f2u(b.w);
+    const int type = meta_type(meta);
+    float3 o, d;
+    object_ray(src, a, b, meta, r, cache, o, d);
+    if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
+        //   X: t from x, (pa, pb) = (y, z);  Y: t from y, (x, z);  Z: t from z, (x, y)
+        const bool ax = type == RTW_PRIM_RECT_X, az = type == RTW_PRIM_RECT_Z;
+        const float on = ax ? o.x : (az ? o.z : o.y), dn = ax ? d.x : (az ? d.z : d.y);
+        const float o1 = ax ? o.y : o.x, d1 = ax ? d.y : d.x;
+        const float o2 = az ? o.y : o.z, d2 = az ? d.y : d.z;
+        return rect_candidate(a, b.x, on, dn, o1, d1, o2, d2, r.tmin, r.tmax, t_out);
+    }
+    if (type == RTW_PRIM_SPHERE || type == RTW_PRIM_MOVING_SPHERE) {
+        float3 c = f3(a);
+        if (type == RTW_PRIM_MOVING_SPHERE) c = moving_center(a, b, src.ext(leaf), r.gather);
+        return sphere_candidate(c, a.w, o, d, r.tmin, r.tmax, t_out);
+    }
+    return medium_candidate(type == RTW_PRIM_VOLUME_BOX, a, b, src.prim_id(leaf), o, d, r, t_out);
+}
+
+// The same function for a leaf index that is UNIFORM over the warp (every lane walks the one
+// leaf range of a small scene in lockstep): the kind and the transform id of the leaf are then
+// warp-uniform, so the dispatch is by branch (no selects, no per-lane decode), and `cur` always
+// holds the ray to test with: the world ray (cur.xf == -1) or its image under transform cur.xf.
+template <class Src>
+RTW_HD void retarget(const Src& src, int xf, const RayW& r, XfRay& cur) {
+    if (xf == cur.xf) return;
+    cur.xf = xf;
+    if (xf >= 0) {
+        float4 r0, r1, r2;
+        src.w2o(xf, r0, r1, r2);
+        cur.o = xform_point(r0, r1, r2, r.o);
+        cur.d = xform_vector(r0, r1, r2, r.d);
+    } else {
+        cur.o = r.o;
+        cur.d = r.d;
+    }
+}
+template <class Src>
+RTW_HD bool prim_candidate_uniform(const Src& src, uint32_t leaf, const RayW& r, XfRay& cur, float& t_out) {
+    float4 a, b;
+    src.prim(leaf, a, b);
+    const uint32_t meta = f2u(b.w);
+    const int type = meta_type(meta);
+    if (type == RTW_PRIM_MOVING_SPHERE) {
+        const float3 o = r.o - motion_translation(a, b, r.time);
+        return sphere_candidate(moving_center(a, b, src.ext(leaf), r.gather), a.w, o, r.d, r.tmin, r.tmax, t_out);
+    }
+    retarget(src, meta_xform(meta), r, cur);
+    const float3 o = cur.o, d = cur.d;
+    if (type == RTW_PRIM_RECT_X) return rect_candidate(a, b.x, o.x, d.x, o.y, d.y, o.z, d.z, r.tmin, r.tmax, t_out);
+    if (type == RTW_PRIM_RECT_Y) return rect_candidate(a, b.x, o.y, d.y, o.x, d.x, o.z, d.z, r.tmin, r.tmax, t_out);
+    if (type == RTW_PRIM_RECT_Z) return rect_candidate(a, b.x, o.z, d.z, o.x, d.x, o.y, d.y, r.tmin, r.tmax, t_out);
+    if (type == RTW_PRIM_SPHERE) return sphere_candidate(f3(a), a.w, o, d, r.tmin, r.tmax, t_out);
+    return medium_candidate(type == RTW_PRIM_VOLUME_BOX, a, b, src.prim_id(leaf), o, d, r, t_out);
 }
 
 struct HitAttr {    // HitRecord, lib/raydata.cuh:117-124
@@ -226,7 +304,7 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
     float3 o, d;
     XfRay cache;
     cache.xf = -1;
-    object_ray<Mem>(sc, a, b, meta, r, cache, o, d);
+    object_ray(SrcScene<Mem>{sc}, a, b, meta, r, cache, o, d);
     const int xf = (type == RTW_PRIM_MOVING_SPHERE) ? -1 : meta_xform(meta);
     float4 w0, w1, w2, q0, q1, q2;  // world→object rows, object→world rows
     if (xf >= 0) {

@@ -88,6 +88,21 @@ struct DScene {
     float cam_lens_radius, cam_time0, cam_time1;
 };
 
+// A scene of <= RTW_SMALL_MAX leaves (the Cornell scenes of the reference: 13 and 8 primitives) is
+// ONE leaf range, walked by every ray in the same order.  Its leaf records travel to the traversal
+// kernels BY VALUE as a kernel parameter: the loop counter over the leaves is warp-uniform, so the
+// records are read through the constant bank into uniform registers, the kind / transform dispatch
+// is a uniform branch, and no lane spends a load or a decode on them.
+#define RTW_SMALL_MAX 16
+struct SmallScene {
+    float4 prim[2 * RTW_SMALL_MAX];   // DScene::prims of leaf i
+    float4 w2o[3 * RTW_SMALL_MAX];    // world→object rows of transform j (first half of DScene::xforms)
+    float2 ext[RTW_SMALL_MAX];        // DScene::prim_ext
+    int32_t prim_id[RTW_SMALL_MAX];   // DScene::leaf_prim
+    int32_t n;                        // leaves
+    int32_t pad[3];
+};
+
 // ---- wavefront state: structure of arrays over P path slots ---------------
 // bytes per slot: ray 32 + hit 8 + throughput/seed 16 + radiance/pixel 16 + misc 8 = 80
 #define RTW_ST_EMPTY 0u

@@ -114,7 +114,7 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
         for (uint32_t leaf = first; leaf < end; leaf++) {
             float t;
             if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, leaf, r, xfc, t)) {
+            if (prim_candidate(SrcScene<Mem>{sc}, leaf, r, xfc, t)) {
                 if (!found || t < tb) {
                     found = true;
                     tb = t;
@@ -169,12 +169,60 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
         for (uint32_t leaf = first; leaf < end; leaf++) {
             float t;
             if (kStats) stats->prims++;
-            if (prim_candidate<Mem>(sc, leaf, r, xfc, t)) return true;
+            if (prim_candidate(SrcScene<Mem>{sc}, leaf, r, xfc, t)) return true;
         }
         if (sp == 0) break;
         cur = stack[--sp];
     }
     return false;
+}
+
+// Small scenes (layout.h SmallScene): the one leaf range, leaf by leaf, with a warp-uniform
+// counter.  Same candidates, same lexicographic (t, primitive id) minimum as traverse_closest.
+RTW_HD bool small_closest(const SmallScene& ss, const RayW& r, float& t_best, uint32_t& leaf_best) {
+    const SrcSmall src{ss};
+    XfRay cur;
+    cur.xf = -1;
+    cur.o = r.o;
+    cur.d = r.d;
+    bool found = false;
+    float tb = r.tmax;
+    uint32_t lb = RTW_REF_NONE;
+    for (int leaf = 0; leaf < ss.n; leaf++) {
+        float t;
+        if (prim_candidate_uniform(src, (uint32_t)leaf, r, cur, t)) {
+            if (!found || t < tb) {
+                found = true;
+                tb = t;
+                lb = (uint32_t)leaf;
+            } else if (t == tb && ss.prim_id[leaf] < ss.prim_id[lb]) {
+                lb = (uint32_t)leaf;
+            }
+        }
+    }
+    t_best = tb;
+    leaf_best = lb;
+    return found;
+}
+// Any hit.  The loop stays warp-uniform: a lane that has its answer keeps walking (its result is
+// not changed any more) until every lane of the warp has one.
+RTW_HD bool small_any(const SmallScene& ss, const RayW& r) {
+    const SrcSmall src{ss};
+    XfRay cur;
+    cur.xf = -1;
+    cur.o = r.o;
+    cur.d = r.d;
+    bool hit = false;
+    for (int leaf = 0; leaf < ss.n; leaf++) {
+        float t;
+        if (prim_candidate_uniform(src, (uint32_t)leaf, r, cur, t)) hit = true;
+#if defined(__CUDA_ARCH__)
+        if (__all_sync(0xffffffffu, hit)) break;
+#else
+        if (hit) break;
+#endif
+    }
+    return hit;
 }
 
 }  // namespace rtw
@@ -249,7 +297,7 @@ struct Walker {
         int p = 0;
         while (!done && li < lend && p < max_prims) {
             float t;
-            if (prim_candidate<Mem>(sc, li, r, xfc, t)) {
+            if (prim_candidate(SrcScene<Mem>{sc}, li, r, xfc, t)) {
                 if (kAny) {
                     found = true;
                     done = true;

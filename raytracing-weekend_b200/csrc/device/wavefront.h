@@ -101,22 +101,38 @@ RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsig
 // ---- stage 1: closest-hit traversal + material classification --------------
 // optixTraverse(tmin 1e-6, tmax RT_DEFAULT_MAX), raygen.cu:41-54.  Returns the
 // shading queue class of the slot, or -1 if the slot holds no live path.
+// How a stage finds its hits: the LBVH (global memory, top levels staged by the kernel) or the
+// by-value copy of a small scene.
 template <class Mem>
-RTW_HD int traverse_thread(const DScene& sc, const float4* top, const DWave& w, uint32_t slot) {
+struct TravBvh {
+    const DScene& sc;
+    const float4* top;
+    RTW_HD bool closest(const RayW& r, float& t, uint32_t& leaf) const { return traverse_closest<Mem, false>(sc, top, r, t, leaf, nullptr); }
+    RTW_HD bool any(const RayW& r) const { return traverse_any<Mem, false>(sc, top, r, nullptr); }
+};
+struct TravSmall {
+    const SmallScene& ss;
+    RTW_HD bool closest(const RayW& r, float& t, uint32_t& leaf) const { return small_closest(ss, r, t, leaf); }
+    RTW_HD bool any(const RayW& r) const { return small_any(ss, r); }
+};
+
+// The closest-hit ray of a slot (false: the slot holds no live ray), and what becomes of its result.
+RTW_HD bool closest_ray_of(const DScene& sc, const DWave& w, uint32_t slot, RayW& r) {
     const RayRec ray = w.ray[slot];
     const float4 ro = ray.o, rd = ray.d;
-    if (f2u(ro.w) == RTW_RAY_NONE) return -1;
-    RayW r;
     r.o = f3(ro);
     r.d = f3(rd);
     r.tmin = 1e-6f;
     r.tmax = 1.e27f;  // shaders/appconfig.h:3
     r.time = ro.w;
     r.gather = rd.w;
-    r.seed = sc.has_media ? f2u(w.st[slot].thr.w) : 0u;
-    float t;
-    uint32_t leaf;
-    const bool found = traverse_closest<Mem, false>(sc, top, r, t, leaf, nullptr);
+    r.seed = 0u;
+    if (f2u(ro.w) == RTW_RAY_NONE) return false;
+    if (sc.has_media) r.seed = f2u(w.st[slot].thr.w);
+    return true;
+}
+template <class Mem>
+RTW_HD int closest_result(const DScene& sc, const DWave& w, uint32_t slot, bool found, float t, uint32_t leaf) {
     w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
     if (!found) return RTW_Q_TERMINAL;
     const int mt = meta_mattype(f2u(Mem::ld4(sc.prims + 2 * leaf + 1).w));
@@ -125,6 +141,19 @@ RTW_HD int traverse_thread(const DScene& sc, const float4* top, const DWave& w, 
     if (mt == RTW_MAT_DIELECTRIC) return RTW_Q_DIELECTRIC;
     if (mt == RTW_MAT_ISOTROPIC) return RTW_Q_ISOTROPIC;
     return RTW_Q_TERMINAL;  // diffuse light, normal material
+}
+template <class Mem, class Trav>
+RTW_HD int traverse_thread_with(const DScene& sc, const Trav& trav, const DWave& w, uint32_t slot) {
+    RayW r;
+    if (!closest_ray_of(sc, w, slot, r)) return -1;
+    float t;
+    uint32_t leaf;
+    const bool found = trav.closest(r, t, leaf);
+    return closest_result<Mem>(sc, w, slot, found, t, leaf);
+}
+template <class Mem>
+RTW_HD int traverse_thread(const DScene& sc, const float4* top, const DWave& w, uint32_t slot) {
+    return traverse_thread_with<Mem>(sc, TravBvh<Mem>{sc, top}, w, slot);
 }
 
 // ---- stage 2: shading -------------------------------------------------------
@@ -264,13 +293,11 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
 
 // ---- stage 3: shadow rays ----------------------------------------------------
 // traceOcclusion, shaders/closehit.cu:16-42,97-113: tmin 500e-7, ray time 0.
-template <class Mem>
-RTW_HD void shadow_thread(const DScene& sc, const float4* top, const DWave& w, uint32_t i) {
+RTW_HD void shadow_ray_of(const DScene& sc, const DWave& w, uint32_t i, RayW& r, float4& c, uint32_t& slot) {
     const float4 so = w.sh_o[i];
     const float4 sd = w.sh_d[i];
-    const float4 c = w.sh_c[i];
-    const uint32_t slot = f2u(sd.w);
-    RayW r;
+    c = w.sh_c[i];
+    slot = f2u(sd.w);
     r.o = f3(so);
     r.d = f3(sd);
     r.tmin = 500 * 1.0e-7f;
@@ -278,11 +305,25 @@ RTW_HD void shadow_thread(const DScene& sc, const float4* top, const DWave& w, u
     r.time = 0.0f;
     r.gather = sc.has_motion ? w.ray[slot].d.w : 0.f;
     r.seed = f2u(c.w);
-    if (!traverse_any<Mem, false>(sc, top, r, nullptr)) {
+}
+RTW_HD void shadow_result(const DWave& w, uint32_t slot, float4 c, bool occluded) {
+    if (!occluded) {
         float4 ra = w.rad[slot];
         ra.x += c.x; ra.y += c.y; ra.z += c.z;
         w.rad[slot] = ra;
     }
+}
+template <class Trav>
+RTW_HD void shadow_thread_with(const DScene& sc, const Trav& trav, const DWave& w, uint32_t i) {
+    RayW r;
+    float4 c;
+    uint32_t slot;
+    shadow_ray_of(sc, w, i, r, c, slot);
+    shadow_result(w, slot, c, trav.any(r));
+}
+template <class Mem>
+RTW_HD void shadow_thread(const DScene& sc, const float4* top, const DWave& w, uint32_t i) {
+    shadow_thread_with(sc, TravBvh<Mem>{sc, top}, w, i);
 }
 
 }  // namespace rtw

@@ -56,6 +56,7 @@ struct LaunchCfg {
     bool has_shadow;        // scene has lights → NEE stage runs
     int step_nodes, step_prims, min_active;   // persistent traversal: step bounds, refill threshold
     bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
+    const SmallScene* small; // host copy of a <= RTW_SMALL_MAX-leaf scene passed to the *_small kernels by value (else null)
 };
 cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
 // One wavefront iteration: regen, reset counters, traverse, shade*, shadow.

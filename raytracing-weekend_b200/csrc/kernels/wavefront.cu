@@ -299,6 +299,52 @@ __global__ void __launch_bounds__(kBlock) k_shadow_flat(const DScene sc, const D
     if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
 }
 
+// Small-scene variants (layout.h SmallScene): the leaf records arrive as a kernel parameter, the
+// loop over them is warp-uniform.  Same per-slot work as the flat kernels otherwise.
+// Control flow is kept warp-convergent around the walk (whole 256-slot tiles, a slot without a
+// live ray walks a null ray and drops the result), which is what lets the compiler keep the leaf
+// loop on the uniform datapath.
+__global__ void __launch_bounds__(kBlock) k_traverse_small(const DScene sc, const DWave w, const __grid_constant__ SmallScene ss) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t tiles = ((uint32_t)w.P + kBlock - 1) / kBlock;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t slot = tile * kBlock + threadIdx.x;
+        RayW r;
+        r.o = f3(0.f); r.d = f3(0.f); r.tmin = 1e-6f; r.tmax = 1.e27f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+        bool alive = false;
+        if (slot < (uint32_t)w.P) alive = closest_ray_of(sc, w, slot, r);
+        float t;
+        uint32_t leaf;
+        const bool found = small_closest(ss, r, t, leaf);
+        int cls = -1;
+        if (alive) cls = closest_result<MemGlobal>(sc, w, slot, found, t, leaf);
+        __syncwarp();
+        const uint32_t peers = __match_any_sync(0xffffffffu, cls);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if (cls >= 0 && (int)lane == leader) base = atomicAdd(w.counters + RTW_C_QUEUE0 + cls, (uint32_t)__popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (cls >= 0) w.queue[(size_t)cls * w.P + base + __popc(peers & ((1u << lane) - 1u))] = slot;
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const DWave w, const __grid_constant__ SmallScene ss) {
+    const uint32_t n = w.counters[RTW_C_SHADOW];
+    const uint32_t tiles = (n + kBlock - 1) / kBlock;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t i = tile * kBlock + threadIdx.x;
+        RayW r;
+        r.o = f3(0.f); r.d = f3(0.f); r.tmin = 500 * 1.0e-7f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t slot = 0;
+        const bool valid = i < n;
+        if (valid) shadow_ray_of(sc, w, i, r, c, slot);
+        const bool occluded = small_any(ss, r) || !valid;
+        if (valid) shadow_result(w, slot, c, occluded);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
+}
+
 __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWave w, const WalkCfg wc) {
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
@@ -422,6 +468,35 @@ __global__ void __launch_bounds__(kBlock) k_trace(const DScene sc, const rtw_ray
     }
 }
 
+__global__ void __launch_bounds__(kBlock) k_trace_small(const __grid_constant__ SmallScene ss, const rtw_ray* __restrict__ rays, int n,
+                                                         rtw_hit* __restrict__ hits, int32_t* __restrict__ occluded) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    RayW r;
+    r.o = f3(0.f); r.d = f3(0.f); r.tmin = 0.f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+    if (valid) {
+        const rtw_ray q = rays[i];
+        r.o = f3(q.origin[0], q.origin[1], q.origin[2]);
+        r.d = f3(q.dir[0], q.dir[1], q.dir[2]);
+        r.tmin = q.tmin; r.tmax = q.tmax; r.time = q.time; r.gather = q.gather_time; r.seed = q.seed;
+    }
+    if (hits) {
+        float t;
+        uint32_t leaf;
+        const bool found = small_closest(ss, r, t, leaf);
+        if (valid) {
+            rtw_hit h;
+            h.t = found ? t : 0.f;
+            h.prim = found ? ss.prim_id[leaf] : -1;
+            hits[i] = h;
+        }
+    }
+    if (occluded) {
+        const bool occ = small_any(ss, r) || !valid;
+        if (valid) occluded[i] = occ ? 1 : 0;
+    }
+}
+
 __global__ void k_rng_stream(uint32_t seed0, uint32_t seed1, int n, uint32_t* tea_out, uint32_t* lcg_out,
                              float* rnd_out, uint32_t* xs_out, float* randf_out) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
@@ -498,7 +573,10 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
         if (e != cudaSuccess) return e;
     }
     cfg->grid_logic = resident_grid(k_regen, 0, sms);
-    if (!cfg->walker) {
+    if (cfg->small) {
+        cfg->grid_traverse = resident_grid(k_traverse_small, 0, sms);
+        cfg->grid_shadow = resident_grid(k_shadow_small, 0, sms);
+    } else if (!cfg->walker) {
         cfg->grid_traverse = resident_grid(k_traverse_flat, cfg->smem_top, sms);
         cfg->grid_shadow = resident_grid(k_shadow_flat, cfg->smem_top, sms);
     } else {
@@ -524,7 +602,8 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     k_advance<<<1, 32, 0, s>>>(w);
     l++;
     if (ev) cudaEventRecord(ev[1], s);
-    if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
+    if (cfg.small) k_traverse_small<<<cfg.grid_traverse, kBlock, 0, s>>>(sc, w, *cfg.small);
+    else if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
     else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
     l++;
     if (ev) cudaEventRecord(ev[2], s);
@@ -532,7 +611,8 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     l++;
     if (ev) cudaEventRecord(ev[3], s);
     if (cfg.has_shadow) {
-        if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
+        if (cfg.small) k_shadow_small<<<cfg.grid_shadow, kBlock, 0, s>>>(sc, w, *cfg.small);
+        else if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
         else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
         l++;
     }
@@ -559,6 +639,11 @@ cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg,
     if (n <= 0) return cudaSuccess;
     int grid = (n + kBlock - 1) / kBlock;
     if (grid > cfg.grid_traverse) grid = cfg.grid_traverse;
+    if (cfg.small) {
+        k_trace_small<<<(n + kBlock - 1) / kBlock, kBlock, 0, s>>>(*cfg.small, rays, n, hits, occluded);
+        if (launches) *launches += 1;
+        return cudaGetLastError();
+    }
     cudaError_t e = cudaMemsetAsync(work2, 0, 2 * sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
     k_trace<<<grid, kBlock, cfg.smem_top, s>>>(sc, rays, n, hits, occluded, work2, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});

@@ -156,15 +156,16 @@ def test_profile_option_reports_stage_times(director):
     assert st["traverse_ms"] > 0 and st["shade_ms"] > 0 and st["logic_ms"] > 0
 
 
-@pytest.mark.parametrize("sid,Nx,Ny", [(1, 96, 54), (4, 64, 64)])
+@pytest.mark.parametrize("sid,Nx,Ny", [(0, 64, 64), (3, 48, 48), (1, 96, 54), (4, 64, 64)])
 def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
-    """Flat per-thread traversal kernels vs persistent walkers with dynamic ray fetching, and
+    """Flat per-thread traversal kernels vs the by-value small-scene kernels (scenes of <= 16
+    primitives; the option is ignored elsewhere) vs persistent walkers with dynamic ray fetching, and
     several step / refill settings: the 1 spp image stays bit-exact (closest hit is the minimum
     of (t, primitive id), independent of the order rays and nodes are visited in)."""
     director.init(Nx, Ny, 1)
     ref = None
     try:
-        for opts in ({"walker": 0}, {"walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
+        for opts in ({"walker": 0, "small": 0}, {"walker": 0, "small": 1}, {"walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
                      {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1}):
             for k, v in opts.items():
                 director.set_option(k, v)
@@ -180,5 +181,5 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             rh, _ = o.trace_closest(director.camera_rays(0), 1)
             assert np.array_equal(hits, rh)
     finally:
-        for k, v in {"walker": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
+        for k, v in {"walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
             director.set_option(k, v)
