@@ -5,6 +5,8 @@
 // (Director.cpp:33-104, 951-969; Director.h:120-126): no OptiX context, modules,
 // program groups, pipeline or SBT — the "ABI" towards the device is the DScene
 // struct passed by value to every kernel.
+#include <cstdlib>
+#include <cstdio>
 #include "rtw_ctx.h"
 
 #include <cstring>
@@ -48,6 +50,13 @@ extern "C" int rtw_create(int device, rtw_ctx** out) {
     if (e != cudaSuccess) {
         g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
         return RTW_ERR_CUDA;
+    }
+    if (const char* g = getenv("RTW_L2_FETCH")) {   // experiment knob
+        size_t before = 0, after = 0;
+        cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
+        cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g));
+        cudaDeviceGetLimit(&after, cudaLimitMaxL2FetchGranularity);
+        fprintf(stderr, "rtw: L2 fetch granularity %zu -> %zu\n", before, after);
     }
     rtw_ctx* c = new rtw_ctx();
     c->device = device;

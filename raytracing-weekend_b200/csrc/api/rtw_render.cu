@@ -18,8 +18,7 @@ static int ensure_wave(rtw_ctx* c, int P) {
     c->wave_capacity = 0;
     auto& pool = c->wave_allocs;
     DWave& w = c->wave;
-    RTW_CUDA(c, dalloc(pool, &w.ray, P));
-    RTW_CUDA(c, dalloc(pool, &w.st, P));
+    RTW_CUDA(c, dalloc(pool, &w.rec, P));
     RTW_CUDA(c, dalloc(pool, &w.hit, P));
     RTW_CUDA(c, dalloc(pool, &w.rad, P));
     RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_SLOTS * P));

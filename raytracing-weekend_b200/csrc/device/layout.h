@@ -144,12 +144,15 @@ struct __align__(32) PathRec {
     uint2 misc;         // (depth | state << 8, ray-time seed)
     uint2 spare;        // written as zero so that a store covers the whole sector
 };
+struct __align__(64) SlotRec {   // one 64-byte line per slot: L2 fetches DRAM in 64-byte pairs of sectors (the
+    RayRec ray;                  // default cudaLimitMaxL2FetchGranularity), so a shading warp that gathers ray +
+    PathRec st;                  // path state through queue indices pays for exactly the bytes it uses
+};
 #define RTW_RAY_NONE   0xffffffffu   // RayRec.o.w of a slot without a live ray (a ray time is a number in [0, 1))
 #define RTW_PIXEL_NONE 0xffffffffu   // rad.w of a slot that holds nothing to flush
 
 struct DWave {
-    RayRec*  ray;       // current ray of the slot
-    PathRec* st;        // throughput, seeds, depth
+    SlotRec* rec;       // current ray + path state of the slot
     uint2*  hit;        // (t bits, leaf index or RTW_REF_NONE): written by the traversal in slot order
     float4* rad;        // radiance sum .xyz, pixel index bits (touched only when light is added)
     uint32_t* queue;    // RTW_Q_SLOTS * P slot indices

@@ -44,12 +44,12 @@ RTW_HD void retire_slot(const DWave& w, uint32_t slot) {
     RayRec none;
     none.o = make_float4(0.f, 0.f, 0.f, u2f(RTW_RAY_NONE));
     none.d = make_float4(0.f, 0.f, 0.f, 0.f);
-    w.ray[slot] = none;
+    w.rec[slot].ray = none;
     PathRec st;
     st.thr = make_float4(0.f, 0.f, 0.f, 0.f);
     st.misc = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
     st.spare = make_uint2(0u, 0u);
-    w.st[slot] = st;
+    w.rec[slot].st = st;
     w.rad[slot] = make_float4(0.f, 0.f, 0.f, u2f(RTW_PIXEL_NONE));
 }
 
@@ -90,8 +90,8 @@ RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long or
     return np;
 }
 RTW_HD void store_path(const DWave& w, uint32_t slot, const NewPath& np) {
-    w.ray[slot] = np.ray;
-    w.st[slot] = np.st;
+    w.rec[slot].ray = np.ray;
+    w.rec[slot].st = np.st;
     w.rad[slot] = np.rad;
 }
 RTW_HD void generate_path(const DScene& sc, const DWave& w, uint32_t slot, unsigned long long ordinal) {
@@ -118,7 +118,7 @@ struct TravSmall {
 
 // The closest-hit ray of a slot (false: the slot holds no live ray), and what becomes of its result.
 RTW_HD bool closest_ray_of(const DScene& sc, const DWave& w, uint32_t slot, RayW& r) {
-    const RayRec ray = w.ray[slot];
+    const RayRec ray = w.rec[slot].ray;
     const float4 ro = ray.o, rd = ray.d;
     r.o = f3(ro);
     r.d = f3(rd);
@@ -128,7 +128,7 @@ RTW_HD bool closest_ray_of(const DScene& sc, const DWave& w, uint32_t slot, RayW
     r.gather = rd.w;
     r.seed = 0u;
     if (f2u(ro.w) == RTW_RAY_NONE) return false;
-    if (sc.has_media) r.seed = f2u(w.st[slot].thr.w);
+    if (sc.has_media) r.seed = f2u(w.rec[slot].st.thr.w);
     return true;
 }
 template <class Mem>
@@ -172,8 +172,8 @@ struct ShadowOut {
 template <int kClass, class Mem>
 RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh) {
     sh.emit = false;
-    const RayRec ray = w.ray[slot];
-    const PathRec st = w.st[slot];
+    const RayRec ray = w.rec[slot].ray;
+    const PathRec st = w.rec[slot].st;
     const uint2 hit = w.hit[slot];
     const float4 ro = ray.o, rd = ray.d;
     const float4 th = st.thr;
@@ -276,12 +276,12 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         RayRec next;
         next.o = make_float4(origin.x, origin.y, origin.z, ray_time);
         next.d = make_float4(dir.x, dir.y, dir.z, rd.w);
-        w.ray[slot] = next;
+        w.rec[slot].ray = next;
         PathRec ns;
         ns.thr = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
         ns.misc = make_uint2(misc_pack(depth, state), lseed);
         ns.spare = make_uint2(0u, 0u);
-        w.st[slot] = ns;
+        w.rec[slot].st = ns;
     }
     if (touch_rad) {
         float4 ra = w.rad[slot];
@@ -303,7 +303,7 @@ RTW_HD void shadow_ray_of(const DScene& sc, const DWave& w, uint32_t i, RayW& r,
     r.tmin = 500 * 1.0e-7f;
     r.tmax = so.w;
     r.time = 0.0f;
-    r.gather = sc.has_motion ? w.ray[slot].d.w : 0.f;
+    r.gather = sc.has_motion ? w.rec[slot].ray.d.w : 0.f;
     r.seed = f2u(c.w);
 }
 RTW_HD void shadow_result(const DWave& w, uint32_t slot, float4 c, bool occluded) {

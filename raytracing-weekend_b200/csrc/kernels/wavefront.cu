@@ -109,7 +109,7 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     __device__ uint32_t count() const { return (uint32_t)w.P; }
     __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_CLOSEST; }
     __device__ bool load(uint32_t slot, RayW& r) const {
-        const RayRec ray = w.ray[slot];
+        const RayRec ray = w.rec[slot].ray;
         const float4 ro = ray.o, rd = ray.d;
         if (f2u(ro.w) == RTW_RAY_NONE) return false;
         r.o = f3(ro);
@@ -118,7 +118,7 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
         r.tmax = 1.e27f;   // shaders/appconfig.h:3
         r.time = ro.w;
         r.gather = rd.w;
-        r.seed = sc.has_media ? f2u(w.st[slot].thr.w) : 0u;
+        r.seed = sc.has_media ? f2u(w.rec[slot].st.thr.w) : 0u;
         return true;
     }
     // returns the shading class of the finished slot
@@ -148,7 +148,7 @@ struct ShadowJob {       // stage 3: the NEE rays (closehit.cu:16-42,97-113): tm
         r.tmin = 500 * 1.0e-7f;
         r.tmax = so.w;
         r.time = 0.0f;
-        r.gather = sc.has_motion ? w.ray[f2u(sd.w)].d.w : 0.f;
+        r.gather = sc.has_motion ? w.rec[f2u(sd.w)].ray.d.w : 0.f;
         r.seed = f2u(w.sh_c[i].w);
         return true;
     }

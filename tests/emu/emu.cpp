@@ -283,13 +283,12 @@ extern "C" void emu_trace(const Emu* e, const rtw_ray* rays, int n, rtw_hit* hit
 extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sample_stride, int sample_count,
                           int max_depth, int P, float* accum, unsigned long long* stats /* rays, shadow rays, iterations */) {
     const DScene& sc = e->sc;
-    std::vector<RayRec> ray(P);
-    std::vector<PathRec> st(P);
+    std::vector<SlotRec> rec(P);
     std::vector<float4> rad(P), sh_o(P), sh_d(P), sh_c(P);
     std::vector<uint2> hit(P);
     std::vector<uint32_t> queue((size_t)RTW_Q_SLOTS * P), counters(RTW_C_WORDS, 0);
     DWave w{};
-    w.ray = ray.data(); w.st = st.data(); w.hit = hit.data(); w.rad = rad.data();
+    w.rec = rec.data(); w.hit = hit.data(); w.rad = rad.data();
     w.queue = queue.data(); w.sh_o = sh_o.data(); w.sh_d = sh_d.data(); w.sh_c = sh_c.data();
     w.counters = counters.data(); w.accum = reinterpret_cast<float4*>(accum);
     w.P = P; w.Nx = Nx; w.Ny = Ny; w.max_depth = max_depth;
