@@ -51,13 +51,6 @@ extern "C" int rtw_create(int device, rtw_ctx** out) {
         g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
         return RTW_ERR_CUDA;
     }
-    if (const char* g = getenv("RTW_L2_FETCH")) {   // experiment knob
-        size_t before = 0, after = 0;
-        cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
-        cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g));
-        cudaDeviceGetLimit(&after, cudaLimitMaxL2FetchGranularity);
-        fprintf(stderr, "rtw: L2 fetch granularity %zu -> %zu\n", before, after);
-    }
     rtw_ctx* c = new rtw_ctx();
     c->device = device;
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -402,13 +395,21 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
         SmallScene& ss = c->small;
         memset(&ss, 0, sizeof(ss));
         ss.n = n;
-        float4 xf[6 * RTW_SMALL_MAX];
-        RTW_CUDA(c, cudaMemcpyAsync(ss.prim, b.prims_packed, sizeof(float4) * 2 * n, cudaMemcpyDeviceToHost, c->stream));
-        RTW_CUDA(c, cudaMemcpyAsync(ss.ext, b.prim_ext, sizeof(float2) * n, cudaMemcpyDeviceToHost, c->stream));
-        RTW_CUDA(c, cudaMemcpyAsync(ss.prim_id, b.leaf_prim, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+        float4 xf[6 * RTW_SMALL_MAX], pk[2 * RTW_SMALL_MAX];
+        float2 ext[RTW_SMALL_MAX];
+        int32_t ids[RTW_SMALL_MAX];
+        RTW_CUDA(c, cudaMemcpyAsync(pk, b.prims_packed, sizeof(float4) * 2 * n, cudaMemcpyDeviceToHost, c->stream));
+        RTW_CUDA(c, cudaMemcpyAsync(ext, b.prim_ext, sizeof(float2) * n, cudaMemcpyDeviceToHost, c->stream));
+        RTW_CUDA(c, cudaMemcpyAsync(ids, b.leaf_prim, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
         if (c->n_xforms > 0)
             RTW_CUDA(c, cudaMemcpyAsync(xf, sc.xforms, sizeof(float4) * 6 * c->n_xforms, cudaMemcpyDeviceToHost, c->stream));
         RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int i = 0; i < n; i++) {
+            ss.leaf[i].a = pk[2 * i];
+            ss.leaf[i].b = pk[2 * i + 1];
+            ss.leaf[i].ext = ext[i];
+            ss.leaf[i].prim_id = ids[i];
+        }
         for (int j = 0; j < c->n_xforms; j++)
             for (int k = 0; k < 3; k++) ss.w2o[3 * j + k] = xf[6 * j + k];
         c->cfg.small = &c->small;

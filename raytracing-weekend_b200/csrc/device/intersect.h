@@ -109,12 +109,12 @@ struct SrcScene {
 };
 struct SrcSmall {
     const SmallScene& ss;
-    RTW_HD void prim(uint32_t leaf, float4& a, float4& b) const { a = ss.prim[2 * leaf]; b = ss.prim[2 * leaf + 1]; }
+    RTW_HD void prim(uint32_t leaf, float4& a, float4& b) const { a = ss.leaf[leaf].a; b = ss.leaf[leaf].b; }
     RTW_HD void w2o(int xf, float4& r0, float4& r1, float4& r2) const {
         r0 = ss.w2o[3 * xf]; r1 = ss.w2o[3 * xf + 1]; r2 = ss.w2o[3 * xf + 2];
     }
-    RTW_HD float2 ext(uint32_t leaf) const { return ss.ext[leaf]; }
-    RTW_HD int prim_id(uint32_t leaf) const { return ss.prim_id[leaf]; }
+    RTW_HD float2 ext(uint32_t leaf) const { return ss.leaf[leaf].ext; }
+    RTW_HD int prim_id(uint32_t leaf) const { return ss.leaf[leaf].prim_id; }
 };
 
 // The world ray carried through an instance transform, remembered between the
@@ -131,21 +131,28 @@ struct XfRay {
 // (on, dn), in-plane coordinates from the other two.
 RTW_HD bool rect_candidate(float4 a, float k, float on, float dn, float o1, float d1, float o2, float d2, float tmin,
                            float tmax, float& t_out) {
-    // A path leaving a rect has its origin ON that plane about half of the time, so k - on is
-    // exactly 0 for one primitive per ray; 0 / dn would take the division's out-of-line slow path
-    // (zero numerator) on a few lanes in every iteration.  0 * (+-1) is the same value: +-0 with the
-    // quotient's sign, NaN when dn is 0 or NaN.
+    // The reference: t = (k - on) / dn; reject unless tmin <= t <= tmax (NaN rejected) and the point lies
+    // in [a.x, a.y] x [a.z, a.w] (comparisons with a NaN coordinate pass).  Written without early exits:
+    // a warp walks a leaf range in lockstep and rarely has all 32 lanes failing the same test.
+    //
+    // A path leaving a rect has its origin ON that plane about half of the time, so k - on is exactly 0
+    // for one primitive per ray; 0 / dn = +-0 (NaN when dn is 0 or NaN) would take the division's
+    // out-of-line slow path on a few lanes in every iteration.  Neither +-0 nor NaN lies in [tmin, tmax]
+    // when tmin > 0 (every ray of the path; only test-hook rays may carry tmin <= 0), so the quotient is
+    // not needed then: the lane divides 1 by dn instead and drops the result.
     const float num = k - on;
-    float t;
-    if (num == 0.0f) t = num * ((dn > 0.0f || dn < 0.0f) ? copysignf(1.0f, dn) : NAN);
-    else t = num / dn;
+    const bool on_plane = num == 0.0f;
+    if (on_plane && !(tmin > 0.0f)) {
+        const float t = num * ((dn > 0.0f || dn < 0.0f) ? copysignf(1.0f, dn) : NAN);
+        const float pa = o1 + t * d1, pb = o2 + t * d2;
+        t_out = t;
+        return (t >= tmin) & (t <= tmax) & !((pa < a.x) | (pa > a.y) | (pb < a.z) | (pb > a.w));
+    }
+    const float t = (on_plane ? 1.0f : num) / dn;
     const float pa = o1 + t * d1;
     const float pb = o2 + t * d2;
-    if (t > tmax || t < tmin) return false;
-    if (pa < a.x || pa > a.y || pb < a.z || pb > a.w) return false;
-    if (!(t >= tmin && t <= tmax)) return false;  // rejects NaN
     t_out = t;
-    return true;
+    return !on_plane & (t >= tmin) & (t <= tmax) & !((pa < a.x) | (pa > a.y) | (pb < a.z) | (pb > a.w));
 }
 // geometry/sphere.cu:48-120, geometry/movingSphere.cu:61-135 (centre c already resolved)
 RTW_HD bool sphere_candidate(float3 c, float radius, float3 o, float3 d, float tmin, float tmax, float& t_out) {
@@ -267,17 +274,17 @@ RTW_HD bool prim_candidate_uniform(const Src& src, uint32_t leaf, const RayW& r,
     src.prim(leaf, a, b);
     const uint32_t meta = f2u(b.w);
     const int type = meta_type(meta);
-    if (type == RTW_PRIM_MOVING_SPHERE) {
-        const float3 o = r.o - motion_translation(a, b, r.time);
-        return sphere_candidate(moving_center(a, b, src.ext(leaf), r.gather), a.w, o, r.d, r.tmin, r.tmax, t_out);
+    if (type != RTW_PRIM_MOVING_SPHERE) {
+        retarget(src, meta_xform(meta), r, cur);
+        const float3 o = cur.o, d = cur.d;
+        if (type == RTW_PRIM_RECT_X) return rect_candidate(a, b.x, o.x, d.x, o.y, d.y, o.z, d.z, r.tmin, r.tmax, t_out);
+        if (type == RTW_PRIM_RECT_Y) return rect_candidate(a, b.x, o.y, d.y, o.x, d.x, o.z, d.z, r.tmin, r.tmax, t_out);
+        if (type == RTW_PRIM_RECT_Z) return rect_candidate(a, b.x, o.z, d.z, o.x, d.x, o.y, d.y, r.tmin, r.tmax, t_out);
+        if (type == RTW_PRIM_SPHERE) return sphere_candidate(f3(a), a.w, o, d, r.tmin, r.tmax, t_out);
+        return medium_candidate(type == RTW_PRIM_VOLUME_BOX, a, b, src.prim_id(leaf), o, d, r, t_out);
     }
-    retarget(src, meta_xform(meta), r, cur);
-    const float3 o = cur.o, d = cur.d;
-    if (type == RTW_PRIM_RECT_X) return rect_candidate(a, b.x, o.x, d.x, o.y, d.y, o.z, d.z, r.tmin, r.tmax, t_out);
-    if (type == RTW_PRIM_RECT_Y) return rect_candidate(a, b.x, o.y, d.y, o.x, d.x, o.z, d.z, r.tmin, r.tmax, t_out);
-    if (type == RTW_PRIM_RECT_Z) return rect_candidate(a, b.x, o.z, d.z, o.x, d.x, o.y, d.y, r.tmin, r.tmax, t_out);
-    if (type == RTW_PRIM_SPHERE) return sphere_candidate(f3(a), a.w, o, d, r.tmin, r.tmax, t_out);
-    return medium_candidate(type == RTW_PRIM_VOLUME_BOX, a, b, src.prim_id(leaf), o, d, r, t_out);
+    const float3 o = r.o - motion_translation(a, b, r.time);
+    return sphere_candidate(moving_center(a, b, src.ext(leaf), r.gather), a.w, o, r.d, r.tmin, r.tmax, t_out);
 }
 
 struct HitAttr {    // HitRecord, lib/raydata.cuh:117-124

@@ -94,11 +94,15 @@ struct DScene {
 // records are read through the constant bank into uniform registers, the kind / transform dispatch
 // is a uniform branch, and no lane spends a load or a decode on them.
 #define RTW_SMALL_MAX 16
+struct SmallLeaf {
+    float4 a, b;                      // DScene::prims of the leaf
+    float2 ext;                       // DScene::prim_ext
+    int32_t prim_id;                  // DScene::leaf_prim
+    int32_t pad;
+};
 struct SmallScene {
-    float4 prim[2 * RTW_SMALL_MAX];   // DScene::prims of leaf i
+    SmallLeaf leaf[RTW_SMALL_MAX];
     float4 w2o[3 * RTW_SMALL_MAX];    // world→object rows of transform j (first half of DScene::xforms)
-    float2 ext[RTW_SMALL_MAX];        // DScene::prim_ext
-    int32_t prim_id[RTW_SMALL_MAX];   // DScene::leaf_prim
     int32_t n;                        // leaves
     int32_t pad[3];
 };

@@ -195,7 +195,7 @@ RTW_HD bool small_closest(const SmallScene& ss, const RayW& r, float& t_best, ui
                 found = true;
                 tb = t;
                 lb = (uint32_t)leaf;
-            } else if (t == tb && ss.prim_id[leaf] < ss.prim_id[lb]) {
+            } else if (t == tb && ss.leaf[leaf].prim_id < ss.leaf[lb].prim_id) {
                 lb = (uint32_t)leaf;
             }
         }

@@ -169,12 +169,26 @@ struct ShadowOut {
 // (miss/miss.cu:23-30) followed by the tail of the rayColor loop body
 // (raygen.cu:60-83: accumulate, continue/terminate, Russian roulette, depth++).
 // Returns true iff the path ended here (the slot goes to the regen queue).
+// `ahead`: a slot this thread will shade later (or RTW_REF_NONE).  Its record and hit are requested
+// into L2 right after this slot's own loads are issued, so the DRAM latency of the gather through
+// the queue index is paid while this vertex is shaded.
+RTW_HD void prefetch_slot(const DWave& w, uint32_t ahead) {
+#if defined(__CUDA_ARCH__)
+    if (ahead != RTW_REF_NONE) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(w.rec + ahead));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(w.hit + ahead));
+    }
+#else
+    (void)w; (void)ahead;
+#endif
+}
 template <int kClass, class Mem>
-RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh) {
+RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, ShadowOut& sh, uint32_t ahead = RTW_REF_NONE) {
     sh.emit = false;
     const RayRec ray = w.rec[slot].ray;
     const PathRec st = w.rec[slot].st;
     const uint2 hit = w.hit[slot];
+    prefetch_slot(w, ahead);
     const float4 ro = ray.o, rd = ray.d;
     const float4 th = st.thr;
     float4 ra = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -355,18 +355,13 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
 // ---------------------------------------------------------------------------
 // One 256-wide chunk [i0, i0 + 256) of shading queue kClass: every warp runs ONE BSDF.
 template <int kClass>
-__device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, uint32_t i0, uint32_t n) {
+__device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, uint32_t slot, uint32_t ahead) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t i = i0 + threadIdx.x;
-    const uint32_t* q = w.queue + (size_t)kClass * w.P;
     ShadowOut sh;
     sh.emit = false;
     bool finished = false;
-    uint32_t slot = 0;
-    if (i < n) {
-        slot = q[i];
-        finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh);
-    }
+    if (slot != RTW_REF_NONE) finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh, ahead);
+    else prefetch_slot(w, ahead);
     __syncwarp();
     queue_push(w, RTW_Q_REGEN, finished, slot);
     if (kClass == RTW_Q_LAMBERTIAN) {
@@ -399,12 +394,24 @@ __global__ void __launch_bounds__(kBlock, 2) k_shade_all(const DScene sc, const 
         n[c] = (class_mask >> c) & 1u ? w.counters[RTW_C_QUEUE0 + c] : 0u;
         first_chunk[c + 1] = first_chunk[c] + (n[c] + kBlock - 1) / kBlock;
     }
+    // this thread's queue entry of chunk v (RTW_REF_NONE past the end of its queue)
+    auto entry = [&](uint32_t v) -> uint32_t {
+        if (v >= first_chunk[RTW_Q_COUNT]) return RTW_REF_NONE;
+        int c = 0;
+#pragma unroll
+        for (int k = 1; k < RTW_Q_COUNT; k++) c += (v >= first_chunk[k]) ? 1 : 0;
+        const uint32_t i = (v - first_chunk[c]) * kBlock + threadIdx.x;
+        return i < n[c] ? w.queue[(size_t)c * w.P + i] : RTW_REF_NONE;
+    };
+    uint32_t slot = entry(blockIdx.x);
     for (uint32_t v = blockIdx.x; v < first_chunk[RTW_Q_COUNT]; v += gridDim.x) {
-        if (v < first_chunk[1]) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, (v - first_chunk[0]) * kBlock, n[0]);
-        else if (v < first_chunk[2]) shade_chunk<RTW_Q_METAL>(sc, w, (v - first_chunk[1]) * kBlock, n[1]);
-        else if (v < first_chunk[3]) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, (v - first_chunk[2]) * kBlock, n[2]);
-        else if (v < first_chunk[4]) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, (v - first_chunk[3]) * kBlock, n[3]);
-        else shade_chunk<RTW_Q_TERMINAL>(sc, w, (v - first_chunk[4]) * kBlock, n[4]);
+        const uint32_t ahead = entry(v + gridDim.x);   // requested now, used by the prefetch inside the chunk
+        if (v < first_chunk[1]) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, slot, ahead);
+        else if (v < first_chunk[2]) shade_chunk<RTW_Q_METAL>(sc, w, slot, ahead);
+        else if (v < first_chunk[3]) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, slot, ahead);
+        else if (v < first_chunk[4]) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, slot, ahead);
+        else shade_chunk<RTW_Q_TERMINAL>(sc, w, slot, ahead);
+        slot = ahead;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // ray statistics of this iteration: every queued slot was one closest-hit ray (the shadow
@@ -487,7 +494,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_small(const __grid_constant__ 
         if (valid) {
             rtw_hit h;
             h.t = found ? t : 0.f;
-            h.prim = found ? ss.prim_id[leaf] : -1;
+            h.prim = found ? ss.leaf[leaf].prim_id : -1;
             hits[i] = h;
         }
     }
