@@ -335,11 +335,11 @@ def main():
             stages[name]["traffic"] = traffic_tab.get(name)
         # the dominant kernel is the stage with the largest share of the frame
         dom = max(stages, key=lambda k: stages[k]["ms_per_iteration"])
-        d = stages[dom]
-        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": d["gbs"], "peak": peak, "unit": "GB/s",
-                            "frac": d["frac"], "traffic": d["traffic"], "peak_source": peak_src,
-                            "bytes_per_unit": d["bytes_per_unit"], "units_per_launch": d["units_per_iteration"],
-                            "avg_launch_ms": d["ms_per_iteration"],
+        ds = stages[dom]
+        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ds["gbs"], "peak": peak, "unit": "GB/s",
+                            "frac": ds["frac"], "traffic": ds["traffic"], "peak_source": peak_src,
+                            "bytes_per_unit": ds["bytes_per_unit"], "units_per_launch": ds["units_per_iteration"],
+                            "avg_launch_ms": ds["ms_per_iteration"],
                             "traversal_on_chip_bytes_per_ray_survey_8d": onchip_per_ray + 96.0,
                             "traversal_on_chip_gbs": agg["rays"] * onchip_per_ray / max(trav_s, 1e-9) / 1e9,
                             "note": "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured "
