@@ -289,13 +289,15 @@ def main():
         value = paths / (dev_ms * 1e-3) / 1e6
         e2e = paths / (e2e_ms * 1e-3) / 1e6
         peak, peak_src = measured_peaks()
+        # pool size: the library's rule (api/rtw_render.cu) unless --pool overrides
+        pool = args.pool or ((1 << 22) if NX * NY * ((spp + world - 1) // world) >= (1 << 28) else (1 << 21))
         line = {"metric": METRIC, "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD if spp == SPP else WORKLOAD.replace("1024 spp", "%d spp (override)" % spp),
                            "parallelism": "sample-sharded x%d, one NCCL reduce per frame" % world,
-                           "l2_policy": "inputs larger than L2: the wavefront pool (2^21 path slots x 160 B state + queues = 336 MB) "
-                                        "streams through HBM every iteration, no flush between steps",
+                           "l2_policy": "inputs larger than L2: the wavefront pool (%d path slots per GPU x 160 B state + queues = %d MB) "
+                                        "streams through HBM every iteration, no flush between steps" % (pool, pool * 160 >> 20),
                            "wall_ms_per_step": wall / args.steps * 1e3},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},

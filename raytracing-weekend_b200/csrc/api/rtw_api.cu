@@ -95,7 +95,7 @@ extern "C" int rtw_destroy(rtw_ctx* c) {
 extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return RTW_ERR_INVALID;
     if (!strcmp(name, "pool_paths")) {
-        if (value < 1024 || value > (1ll << 26)) return fail(c, RTW_ERR_INVALID, "pool_paths out of range [1024, 2^26]");
+        if (value != 0 && (value < 1024 || value > (1ll << 26))) return fail(c, RTW_ERR_INVALID, "pool_paths out of range [1024, 2^26] (0 = auto)");
         c->opt_pool_paths = value;
     } else if (!strcmp(name, "top_nodes")) {
         if (value < 0 || value > 3584) return fail(c, RTW_ERR_INVALID, "top_nodes out of range [0, 3584]");

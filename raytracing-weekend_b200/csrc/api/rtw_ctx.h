@@ -42,7 +42,7 @@ struct rtw_ctx {
     int frame_spp = 0;
 
     // ---- options ----
-    long long opt_pool_paths = 1 << 21;
+    long long opt_pool_paths = 0;    // 0 = auto (rtw_render.cu)
     int opt_top_nodes = 1024;
     int opt_leaf_size = 0;
     int opt_small = -1;              // -1 = auto, 0 = never, 1 = whenever the scene qualifies

@@ -313,6 +313,10 @@ __global__ void __launch_bounds__(kBlock) k_traverse_small(const DScene sc, cons
         r.o = f3(0.f); r.d = f3(0.f); r.tmin = 1e-6f; r.tmax = 1.e27f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
         bool alive = false;
         if (slot < (uint32_t)w.P) alive = closest_ray_of(sc, w, slot, r);
+        // warp-uniform: a warp of empty slots walks nothing.  (Packing the live rays of a tile into fewer warps
+        // was tried for the drain tail of a frame and is slower: one warp's walk is a ~1400-instruction
+        // dependent chain, so a tile takes as long with one walking warp as with eight.)
+        if (!__any_sync(0xffffffffu, alive)) continue;
         float t;
         uint32_t leaf;
         const bool found = small_closest(ss, r, t, leaf);
