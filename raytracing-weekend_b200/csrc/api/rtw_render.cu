@@ -97,7 +97,17 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             c->prof_events.push_back(e);
         }
     }
+    // Sparse mode: once the counters show fewer than half of the slots with a ray in flight (the drain tail of
+    // the frame, or a frame smaller than the pool), the small-scene traversal walks a list of those slots —
+    // kept by the shading and regeneration kernels from one iteration earlier — instead of scanning the pool.
+    bool sparse = false, filled_prev = false;
+    w.trace_fill = 0;
+    w.trace_use = 0;
     while (!done) {
+        w.parity = (int)(iter & 1);
+        w.trace_fill = (sparse && c->cfg.small) ? 1 : 0;
+        w.trace_use = (w.trace_fill && filled_prev) ? 1 : 0;
+        filled_prev = w.trace_fill != 0;
         cudaEvent_t* sev = nullptr;
         if (c->opt_profile && sampled < kMaxSampled && iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
         RTW_CUDA(c, wavefront_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
@@ -110,6 +120,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             RTW_CUDA(c, cudaEventSynchronize(c->ring_events[j % 8]));
             const uint32_t* s = c->h_counters + (j % 8) * RTW_C_WORDS;
             if (s[RTW_C_ALIVE] == 0) done = true;
+            if (s[RTW_C_ALIVE] < (uint32_t)(P / 2)) sparse = true;
         }
         if (iter > (1ull << 40)) return fail(c, RTW_ERR_STATE, "wavefront did not terminate");
     }

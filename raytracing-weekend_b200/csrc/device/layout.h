@@ -121,7 +121,8 @@ struct SmallScene {
 #define RTW_Q_TERMINAL   4   // miss, diffuse light, normal material: path ends
 #define RTW_Q_COUNT      5   // shading classes
 #define RTW_Q_REGEN      5   // slots whose path finished this iteration: flushed and refilled by k_regen
-#define RTW_Q_SLOTS      6   // queues allocated (RTW_Q_SLOTS * P slot indices)
+#define RTW_Q_TRACE      6   // sparse mode only: the slots that hold a ray to trace in the next traversal
+#define RTW_Q_SLOTS      7   // queues allocated (RTW_Q_SLOTS * P slot indices)
 
 // counters[] layout (uint32 unless noted)
 #define RTW_C_QUEUE0     0                 // RTW_Q_SLOTS queue lengths (5 shading classes + regen)
@@ -133,6 +134,7 @@ struct SmallScene {
 #define RTW_C_PATHS_LO   14                // uint64 paths flushed
 #define RTW_C_WORK_CLOSEST 16              // next pool slot to fetch (persistent traversal warps)
 #define RTW_C_WORK_SHADOW  17              // next shadow-queue entry to fetch
+#define RTW_C_TRACE0     18                // sparse mode: length of the trace list of even / odd iterations (two words)
 #define RTW_C_WORDS      20
 
 // Per-slot state is read and written through queue indices (a warp of the shading kernels holds
@@ -170,6 +172,11 @@ struct DWave {
     int max_depth;
     int sample_first, sample_stride;
     unsigned long long total;   // Nx*Ny*sample_count sample ordinals to issue
+    // Sparse mode (the drain tail of a frame, when most slots are empty; set per iteration by the host):
+    // the slots with a ray to trace are listed instead of found by scanning the pool.
+    int parity;                 // iteration index & 1
+    int trace_fill;             // shading and regeneration list the slots the NEXT / this traversal must trace
+    int trace_use;              // this iteration's traversal walks the list (filled since the previous iteration)
 };
 
 }  // namespace rtw

@@ -33,15 +33,18 @@ __device__ __forceinline__ void stage_top(const DScene& sc, float4* s_top) {
 // ---------------------------------------------------------------------------
 // Warp-aggregated push of `slot` onto queue `cls` for the lanes where `pred` holds:
 // one ballot + one atomicAdd per warp.
-__device__ __forceinline__ void queue_push(const DWave& w, int cls, bool pred, uint32_t slot) {
+__device__ __forceinline__ void queue_push_at(const DWave& w, int queue, int counter, bool pred, uint32_t slot) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t mask = __ballot_sync(0xffffffffu, pred);
     if (!mask) return;
     const int leader = __ffs(mask) - 1;
     uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_QUEUE0 + cls, (uint32_t)__popc(mask));
+    if ((int)lane == leader) base = atomicAdd(w.counters + counter, (uint32_t)__popc(mask));
     base = __shfl_sync(0xffffffffu, base, leader);
-    if (pred) w.queue[(size_t)cls * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
+    if (pred) w.queue[(size_t)queue * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
+}
+__device__ __forceinline__ void queue_push(const DWave& w, int cls, bool pred, uint32_t slot) {
+    queue_push_at(w, cls, RTW_C_QUEUE0 + cls, pred, slot);
 }
 
 // Regeneration: the slots whose path finished in the previous iteration (a compact
@@ -52,6 +55,8 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
     const uint32_t n = w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
     const unsigned long long next = *reinterpret_cast<const unsigned long long*>(w.counters + RTW_C_NEXT_LO);
     const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
+    // sparse mode: the restarted slots follow the survivors that the shading kernel listed (k_advance adds the count)
+    const uint32_t trace_base = w.trace_fill ? w.counters[RTW_C_TRACE0 + w.parity] : 0u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const uint32_t slot = q[i];
         // the old path's state is requested first, the new path (tea<64>: ~1000 integer instructions,
@@ -64,6 +69,7 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
             const NewPath np = make_path(sc, w, ordinal);
             logic_flush(w, ra);
             store_path(w, slot, np);
+            if (w.trace_fill) w.queue[(size_t)RTW_Q_TRACE * w.P + trace_base + i] = slot;
         } else {
             logic_flush(w, ra);
             retire_slot(w, slot);
@@ -76,7 +82,13 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
 __global__ void k_advance(const DWave w) {
     if (threadIdx.x == 0) {
         unsigned long long* next = reinterpret_cast<unsigned long long*>(w.counters + RTW_C_NEXT_LO);
-        *next += (unsigned long long)w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+        const unsigned long long n = (unsigned long long)w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+        if (w.trace_fill) {   // paths k_regen just started (ordinals next .. total - 1 of the n it looked at)
+            const unsigned long long left = *next < w.total ? w.total - *next : 0ull;
+            w.counters[RTW_C_TRACE0 + w.parity] += (uint32_t)(n < left ? n : left);
+            w.counters[RTW_C_TRACE0 + (w.parity ^ 1)] = 0u;   // filled by this iteration's shading for the next one
+        }
+        *next += n;
     }
     __syncwarp();
     if (threadIdx.x < 8) w.counters[threadIdx.x] = 0u;
@@ -306,13 +318,19 @@ __global__ void __launch_bounds__(kBlock) k_shadow_flat(const DScene sc, const D
 // loop on the uniform datapath.
 __global__ void __launch_bounds__(kBlock) k_traverse_small(const DScene sc, const DWave w, const __grid_constant__ SmallScene ss) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t tiles = ((uint32_t)w.P + kBlock - 1) / kBlock;
+    // the whole pool in slot order, or (sparse mode) the list of slots that hold a ray
+    const uint32_t n = w.trace_use ? w.counters[RTW_C_TRACE0 + w.parity] : (uint32_t)w.P;
+    const uint32_t* list = w.queue + (size_t)RTW_Q_TRACE * w.P;
+    const uint32_t tiles = (n + kBlock - 1) / kBlock;
     for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const uint32_t slot = tile * kBlock + threadIdx.x;
+        uint32_t slot = tile * kBlock + threadIdx.x;
         RayW r;
         r.o = f3(0.f); r.d = f3(0.f); r.tmin = 1e-6f; r.tmax = 1.e27f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
         bool alive = false;
-        if (slot < (uint32_t)w.P) alive = closest_ray_of(sc, w, slot, r);
+        if (slot < n) {
+            if (w.trace_use) slot = list[slot];
+            alive = closest_ray_of(sc, w, slot, r);
+        }
         // warp-uniform: a warp of empty slots walks nothing.  (Packing the live rays of a tile into fewer warps
         // was tried for the drain tail of a frame and is slower: one warp's walk is a ~1400-instruction
         // dependent chain, so a tile takes as long with one walking warp as with eight.)
@@ -368,6 +386,7 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
     else prefetch_slot(w, ahead);
     __syncwarp();
     queue_push(w, RTW_Q_REGEN, finished, slot);
+    if (w.trace_fill) queue_push_at(w, RTW_Q_TRACE, RTW_C_TRACE0 + (w.parity ^ 1), slot != RTW_REF_NONE && !finished, slot);
     if (kClass == RTW_Q_LAMBERTIAN) {
         const uint32_t mask = __ballot_sync(0xffffffffu, sh.emit);
         if (mask) {

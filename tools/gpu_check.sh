@@ -6,5 +6,5 @@ echo "== pytest -m gpu"; timeout 1500 python -m pytest tests -q -m gpu > gpurun_
 echo "== smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -3 gpurun_out/smoke.log
 echo "== bench"; timeout 900 python bench.py --steps ${STEPS:-3} --warmup ${WARMUP:-3} > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 if [ -n "$NCU_LIST" ]; then
-  echo "== ncu launch list"; timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 0 --spp 16 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu exit $?"; tail -3 gpurun_out/ncu_list.log
+  echo "== ncu launch list"; timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 0 --spp 128 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu exit $?"; tail -3 gpurun_out/ncu_list.log
 fi
