@@ -6,7 +6,7 @@ txt = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "raytracing-weeke
                      capture_output=True, text=True, check=True).stdout
 out = os.path.join(ROOT, "profiles", "sass")
 os.makedirs(out, exist_ok=True)
-keep = {"k_traverse_flat", "k_shadow_flat", "k_traverse", "k_shadow", "k_shade_all", "k_regen", "k_advance", "k_karras",
+keep = {"k_traverse_small", "k_shadow_small", "k_traverse_flat", "k_shadow_flat", "k_traverse", "k_shadow", "k_shade_all", "k_regen", "k_advance", "k_karras",
         "k_refit", "k_sort_scatter", "k_morton", "k_prim_aabb", "k_tonemap", "k_trace"}
 index = []
 for p in re.split(r"\n\s*Function : ", txt)[1:]:
@@ -22,5 +22,10 @@ with open(os.path.join(out, "INDEX.md"), "w") as f:
     f.write("# SASS listings (cuobjdump -sass librtw.so, sm_100a, nvcc 12.9, -O3 -lineinfo -fmad=false)\n\n"
             "Instruction counts per kernel; full text for the hot kernels beside this file (encodings stripped).\n"
             "No tcgen05 / UTMA instructions are expected: the path has no dense contraction (BASELINE.json north_star).\n\n"
-            "| kernel | SASS instructions |\n|---|---|\n" + "\n".join("| %s | %d |" % x for x in index) + "\n")
+            "| kernel | SASS instructions |\n|---|---|\n" + "\n".join("| %s | %d |" % x for x in index) + "\n\n"
+            "Mnemonics the design relies on (grep the listings): `LDG.E.ENL2.256` / `STG.E.ENL2.256` (one 256-bit access per\n"
+            "32-byte half of a slot record: k_shade_all, k_regen, k_traverse_small), `REDG.E.ADD.F32x4` (accumulator flush,\n"
+            "k_regen), `MATCH.ANY` (one atomic round trip per warp for all queue classes), `LDCU` / `BRA.U` / `BRXU` (the\n"
+            "leaf loop of k_traverse_small / k_shadow_small runs on the uniform datapath: leaf records come from the\n"
+            "kernel-parameter bank), `CCTL.E.PF2` (`prefetch.global.L2` of the next chunk's records, k_shade_all).\n")
 print(index)
