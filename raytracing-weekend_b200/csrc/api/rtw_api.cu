@@ -115,6 +115,9 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "walker")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "walker out of range [-1, 1]");
         c->opt_walker = (int)value;
+    } else if (!strcmp(name, "shade_ctas")) {
+        if (value < 2 || value > 4) return fail(c, RTW_ERR_INVALID, "shade_ctas out of range [2, 4]");
+        c->opt_shade_ctas = (int)value;
     } else if (!strcmp(name, "profile")) {
         c->opt_profile = value ? 1 : 0;
     } else if (!strcmp(name, "lag")) {
@@ -391,6 +394,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // Small scenes (one leaf range, <= RTW_SMALL_MAX leaves and transforms): the leaf records go to
     // the traversal kernels by value.
     c->cfg.small = nullptr;
+    c->cfg.shade_ctas = c->opt_shade_ctas;
     if (c->opt_small != 0 && !(c->opt_walker == 1) && (sc.root & RTW_REF_LEAF) && n <= RTW_SMALL_MAX && c->n_xforms <= RTW_SMALL_MAX) {
         SmallScene& ss = c->small;
         memset(&ss, 0, sizeof(ss));

@@ -308,21 +308,32 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
     const float4 b = Mem::ld4(sc.prims + 2 * leaf + 1);
     const uint32_t meta = f2u(b.w);
     const int type = meta_type(meta);
-    float3 o, d;
-    XfRay cache;
-    cache.xf = -1;
-    object_ray(SrcScene<Mem>{sc}, a, b, meta, r, cache, o, d);
     const int xf = (type == RTW_PRIM_MOVING_SPHERE) ? -1 : meta_xform(meta);
-    float4 w0, w1, w2, q0, q1, q2;  // world→object rows, object→world rows
-    if (xf >= 0) {
-        const float4* m = sc.xforms + 6 * xf;
-        w0 = Mem::ld4(m); w1 = Mem::ld4(m + 1); w2 = Mem::ld4(m + 2);
-        q0 = Mem::ld4(m + 3); q1 = Mem::ld4(m + 4); q2 = Mem::ld4(m + 5);
+    // The transform rows are loaded where they are used (and the world→object rows a second time for the
+    // normal, an L1 hit) instead of living in twelve registers across the whole function: untransformed
+    // primitives are the common case and the shading kernel is register-bound.
+    const float4* m = sc.xforms + 6 * (xf >= 0 ? xf : 0);
+    float3 o = r.o, d = r.d;   // object_ray()
+    if (type == RTW_PRIM_MOVING_SPHERE) {
+        o = r.o - motion_translation(a, b, r.time);
+    } else if (xf >= 0) {
+        const float4 w0 = Mem::ld4(m), w1 = Mem::ld4(m + 1), w2 = Mem::ld4(m + 2);
+        o = xform_point(w0, w1, w2, r.o);
+        d = xform_vector(w0, w1, w2, r.d);
     }
     float3 pobj = o + t * d;
-    float3 point;
-    if (type == RTW_PRIM_MOVING_SPHERE) point = pobj + motion_translation(a, b, r.time);
-    else point = (xf >= 0) ? xform_point(q0, q1, q2, pobj) : pobj;
+    float3 point = pobj;
+    if (type == RTW_PRIM_MOVING_SPHERE) {
+        point = pobj + motion_translation(a, b, r.time);
+    } else if (xf >= 0) {
+        const float4 q0 = Mem::ld4(m + 3), q1 = Mem::ld4(m + 4), q2 = Mem::ld4(m + 5);
+        point = xform_point(q0, q1, q2, pobj);
+    }
+    auto normal_to_world = [&](float3 n) -> float3 {
+        if (xf < 0) return n;
+        const float4 w0 = Mem::ld4(m), w1 = Mem::ld4(m + 1), w2 = Mem::ld4(m + 2);
+        return xform_normal(w0, w1, w2, n);
+    };
     h.point = point;
     h.u = 0.f;
     h.v = 0.f;
@@ -338,8 +349,7 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
             c = moving_center(a, b, times, r.gather);
         }
         float3 n = (point - c) / a.w;
-        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
-        h.normal = n;
+        h.normal = normal_to_world(n);
         if (want_uv) get_sphere_uv(n, h.u, h.v);
     } else if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
         float pa, pb;
@@ -348,16 +358,14 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
         else if (type == RTW_PRIM_RECT_Y) { pa = o.x + t * d.x; pb = o.z + t * d.z; n = f3(0.f, 1.f, 0.f); }
         else { pa = o.x + t * d.x; pb = o.y + t * d.y; n = f3(0.f, 0.f, 1.f); }
         if (meta_flip(meta)) n = -n;
-        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
-        h.normal = normalize(n);
+        h.normal = normalize(normal_to_world(n));
         if (want_uv) {   // (u, v) only feed image textures (texture/imageTexture.cu:15); checker and noise use the point
             h.u = (pa - a.x) / (a.y - a.x);
             h.v = (pb - a.z) / (a.w - a.z);
         }
     } else {  // volumes: normal (1,0,0), uv 0 (volumeBox.cu:88-93, volumeSphere.cu:99-105)
         float3 n = f3(1.f, 0.f, 0.f);
-        if (xf >= 0) n = xform_normal(w0, w1, w2, n);
-        h.normal = normalize(n);
+        h.normal = normalize(normal_to_world(n));
     }
 }
 

@@ -43,9 +43,6 @@ __device__ __forceinline__ void queue_push_at(const DWave& w, int queue, int cou
     base = __shfl_sync(0xffffffffu, base, leader);
     if (pred) w.queue[(size_t)queue * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
 }
-__device__ __forceinline__ void queue_push(const DWave& w, int cls, bool pred, uint32_t slot) {
-    queue_push_at(w, cls, RTW_C_QUEUE0 + cls, pred, slot);
-}
 
 // Regeneration: the slots whose path finished in the previous iteration (a compact
 // queue, so every lane of a warp does the same work) are flushed into the accumulator
@@ -385,22 +382,28 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
     if (slot != RTW_REF_NONE) finished = shade_thread<kClass, MemGlobal>(sc, w, slot, sh, ahead);
     else prefetch_slot(w, ahead);
     __syncwarp();
-    queue_push(w, RTW_Q_REGEN, finished, slot);
-    if (w.trace_fill) queue_push_at(w, RTW_Q_TRACE, RTW_C_TRACE0 + (w.parity ^ 1), slot != RTW_REF_NONE && !finished, slot);
-    if (kClass == RTW_Q_LAMBERTIAN) {
-        const uint32_t mask = __ballot_sync(0xffffffffu, sh.emit);
-        if (mask) {
-            const int leader = __ffs(mask) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(w.counters + RTW_C_SHADOW, (uint32_t)__popc(mask));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (sh.emit) {
-                const uint32_t pos = base + __popc(mask & ((1u << lane) - 1u));
-                w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
-                w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
-                w.sh_c[pos] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, __uint_as_float(sh.seed));
-            }
-        }
+    // The warp's pushes — finished slots (regen queue), NEE rays (shadow queue), survivors (sparse-mode
+    // trace list) — reserve their space with ONE atomic round trip: lanes 0, 1, 2 each add one count.
+    const bool survivor = w.trace_fill && slot != RTW_REF_NONE && !finished;
+    const uint32_t m_regen = __ballot_sync(0xffffffffu, finished);
+    const uint32_t m_shadow = kClass == RTW_Q_LAMBERTIAN ? __ballot_sync(0xffffffffu, sh.emit) : 0u;
+    const uint32_t m_trace = w.trace_fill ? __ballot_sync(0xffffffffu, survivor) : 0u;
+    if ((m_regen | m_shadow | m_trace) == 0u) return;
+    const uint32_t mine = lane == 0 ? m_regen : (lane == 1 ? m_shadow : m_trace);
+    const int counter = lane == 0 ? RTW_C_QUEUE0 + RTW_Q_REGEN : (lane == 1 ? RTW_C_SHADOW : RTW_C_TRACE0 + (w.parity ^ 1));
+    uint32_t base = 0;
+    if (lane < 3 && mine) base = atomicAdd(w.counters + counter, (uint32_t)__popc(mine));
+    const uint32_t b_regen = __shfl_sync(0xffffffffu, base, 0);
+    const uint32_t b_shadow = __shfl_sync(0xffffffffu, base, 1);
+    const uint32_t b_trace = __shfl_sync(0xffffffffu, base, 2);
+    const uint32_t below = (1u << lane) - 1u;
+    if (finished) w.queue[(size_t)RTW_Q_REGEN * w.P + b_regen + __popc(m_regen & below)] = slot;
+    if (survivor) w.queue[(size_t)RTW_Q_TRACE * w.P + b_trace + __popc(m_trace & below)] = slot;
+    if (kClass == RTW_Q_LAMBERTIAN && sh.emit) {
+        const uint32_t pos = b_shadow + __popc(m_shadow & below);
+        w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
+        w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
+        w.sh_c[pos] = make_float4(sh.contrib.x, sh.contrib.y, sh.contrib.z, __uint_as_float(sh.seed));
     }
 }
 
@@ -409,32 +412,53 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
 // CTAs take chunks round-robin, so a CTA — and every warp in it — runs one BSDF at a time.  The
 // short queues (metal, dielectric, terminal: 5-30 % of the vertices) no longer pay a launch each
 // with the machine mostly idle.
-__global__ void __launch_bounds__(kBlock, 2) k_shade_all(const DScene sc, const DWave w, uint32_t class_mask) {
-    uint32_t n[RTW_Q_COUNT], first_chunk[RTW_Q_COUNT + 1];
-    first_chunk[0] = 0;
-#pragma unroll
-    for (int c = 0; c < RTW_Q_COUNT; c++) {
-        n[c] = (class_mask >> c) & 1u ? w.counters[RTW_C_QUEUE0 + c] : 0u;
-        first_chunk[c + 1] = first_chunk[c] + (n[c] + kBlock - 1) / kBlock;
+// kCtas = resident CTAs per SM the register allocation is held to (option `shade_ctas`): 2 → 95 registers,
+// 3 → 80, 4 → 64; the kernel is bound by memory latency, so warps in flight are what it is short of.
+template <int kCtas>
+__global__ void __launch_bounds__(kBlock, kCtas) k_shade_all(const DScene sc, const DWave w, uint32_t class_mask) {
+    // queue lengths and the first chunk number of every class: shared memory, not registers (the kernel is
+    // register-bound: 128 with the tables in registers and spills, see profiles/sass/INDEX.md)
+    __shared__ uint32_t s_n[RTW_Q_COUNT], s_first[RTW_Q_COUNT + 1];
+    if (threadIdx.x == 0) {
+        uint32_t f = 0;
+        for (int c = 0; c < RTW_Q_COUNT; c++) {
+            const uint32_t n = (class_mask >> c) & 1u ? w.counters[RTW_C_QUEUE0 + c] : 0u;
+            s_n[c] = n;
+            s_first[c] = f;
+            f += (n + kBlock - 1) / kBlock;
+        }
+        s_first[RTW_Q_COUNT] = f;
     }
-    // this thread's queue entry of chunk v (RTW_REF_NONE past the end of its queue)
-    auto entry = [&](uint32_t v) -> uint32_t {
-        if (v >= first_chunk[RTW_Q_COUNT]) return RTW_REF_NONE;
+    __syncthreads();
+    const uint32_t chunks = s_first[RTW_Q_COUNT];
+    // class of chunk v
+    auto class_of = [&](uint32_t v) -> int {
         int c = 0;
 #pragma unroll
-        for (int k = 1; k < RTW_Q_COUNT; k++) c += (v >= first_chunk[k]) ? 1 : 0;
-        const uint32_t i = (v - first_chunk[c]) * kBlock + threadIdx.x;
-        return i < n[c] ? w.queue[(size_t)c * w.P + i] : RTW_REF_NONE;
+        for (int k = 1; k < RTW_Q_COUNT; k++) c += (v >= s_first[k]) ? 1 : 0;
+        return c;
     };
+    // this thread's queue entry of chunk v (RTW_REF_NONE past the end of its queue)
+    auto entry = [&](uint32_t v) -> uint32_t {
+        if (v >= chunks) return RTW_REF_NONE;
+        const int c = class_of(v);
+        const uint32_t i = (v - s_first[c]) * kBlock + threadIdx.x;
+        return i < s_n[c] ? w.queue[(size_t)c * w.P + i] : RTW_REF_NONE;
+    };
+    // Two chunks of queue entries are in flight: `ahead` (loaded one trip ago) addresses the record prefetch
+    // inside the chunk, `ahead2` is requested now — so the prefetch never waits for its own index load.
     uint32_t slot = entry(blockIdx.x);
-    for (uint32_t v = blockIdx.x; v < first_chunk[RTW_Q_COUNT]; v += gridDim.x) {
-        const uint32_t ahead = entry(v + gridDim.x);   // requested now, used by the prefetch inside the chunk
-        if (v < first_chunk[1]) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, slot, ahead);
-        else if (v < first_chunk[2]) shade_chunk<RTW_Q_METAL>(sc, w, slot, ahead);
-        else if (v < first_chunk[3]) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, slot, ahead);
-        else if (v < first_chunk[4]) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, slot, ahead);
+    uint32_t ahead = entry(blockIdx.x + gridDim.x);
+    for (uint32_t v = blockIdx.x; v < chunks; v += gridDim.x) {
+        const uint32_t ahead2 = entry(v + 2 * gridDim.x);
+        const int c = class_of(v);
+        if (c == RTW_Q_LAMBERTIAN) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, slot, ahead);
+        else if (c == RTW_Q_METAL) shade_chunk<RTW_Q_METAL>(sc, w, slot, ahead);
+        else if (c == RTW_Q_DIELECTRIC) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, slot, ahead);
+        else if (c == RTW_Q_ISOTROPIC) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, slot, ahead);
         else shade_chunk<RTW_Q_TERMINAL>(sc, w, slot, ahead);
         slot = ahead;
+        ahead = ahead2;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // ray statistics of this iteration: every queued slot was one closest-hit ray (the shadow
@@ -613,7 +637,8 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
         cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
         cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
     }
-    cfg->grid_shade = resident_grid(k_shade_all, 0, sms);
+    cfg->grid_shade = cfg->shade_ctas == 2 ? resident_grid(k_shade_all<2>, 0, sms)
+                    : cfg->shade_ctas == 4 ? resident_grid(k_shade_all<4>, 0, sms) : resident_grid(k_shade_all<3>, 0, sms);
     return cudaSuccess;
 }
 
@@ -637,7 +662,10 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
     l++;
     if (ev) cudaEventRecord(ev[2], s);
-    k_shade_all<<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, cfg.class_mask | (1u << RTW_Q_TERMINAL));
+    const uint32_t classes = cfg.class_mask | (1u << RTW_Q_TERMINAL);
+    if (cfg.shade_ctas == 2) k_shade_all<2><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
+    else if (cfg.shade_ctas == 4) k_shade_all<4><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
+    else k_shade_all<3><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
     l++;
     if (ev) cudaEventRecord(ev[3], s);
     if (cfg.has_shadow) {
