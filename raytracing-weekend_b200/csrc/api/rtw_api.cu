@@ -7,6 +7,7 @@
 // struct passed by value to every kernel.
 #include <cstdlib>
 #include <cstdio>
+#include <algorithm>
 #include "rtw_ctx.h"
 
 #include <cstring>
@@ -112,6 +113,8 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "small")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "small out of range [-1, 1]");
         c->opt_small = (int)value;
+    } else if (!strcmp(name, "small_static")) {
+        c->opt_small_static = value ? 1 : 0;   // 0: every record of a small scene goes through the runs (test / comparison)
     } else if (!strcmp(name, "walker")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "walker out of range [-1, 1]");
         c->opt_walker = (int)value;
@@ -408,11 +411,70 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
         if (c->n_xforms > 0)
             RTW_CUDA(c, cudaMemcpyAsync(xf, sc.xforms, sizeof(float4) * 6 * c->n_xforms, cudaMemcpyDeviceToHost, c->stream));
         RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+        // Rects and static spheres go to the static table (layout.h SmallGroup) while its shape has
+        // room: group 0 = untransformed, groups 1.. = the transforms in order of first use.  The rest
+        // stays in records ordered by (transform, kind), cut into runs (layout.h SmallRun).
+        int group_xf[RTW_SS_GROUPS];
+        ss.n_groups = 1;
+        group_xf[0] = -1;
+        int order[RTW_SMALL_MAX], key[RTW_SMALL_MAX], n_left = 0;
         for (int i = 0; i < n; i++) {
-            ss.leaf[i].a = pk[2 * i];
-            ss.leaf[i].b = pk[2 * i + 1];
-            ss.leaf[i].ext = ext[i];
-            ss.leaf[i].prim_id = ids[i];
+            const uint32_t meta = f2u(pk[2 * i + 1].w);
+            const int kind = meta_type(meta);
+            const int xfi = kind == RTW_PRIM_MOVING_SPHERE ? -1 : meta_xform(meta);
+            const bool rect = kind == RTW_PRIM_RECT_X || kind == RTW_PRIM_RECT_Y || kind == RTW_PRIM_RECT_Z;
+            bool placed = false;
+            if (c->opt_small_static && (rect || kind == RTW_PRIM_SPHERE)) {
+                int g = 0;
+                while (g < ss.n_groups && group_xf[g] != xfi) g++;
+                if (g == ss.n_groups && g < RTW_SS_GROUPS) {
+                    group_xf[g] = xfi;
+                    for (int k = 0; k < 3; k++) ss.group[g].w2o[k] = xf[6 * xfi + k];
+                    ss.n_groups++;
+                }
+                if (g < ss.n_groups) {
+                    SmallGroup& sg = ss.group[g];
+                    if (rect) {
+                        const int axis = kind - RTW_PRIM_RECT_X;
+                        if (sg.n_rect[axis] < RTW_SS_RECTS) {
+                            SmallRect& sr = sg.rect[axis][sg.n_rect[axis]++];
+                            sr.a = pk[2 * i];
+                            sr.k = pk[2 * i + 1].x;
+                            sr.prim_id = ids[i];
+                            sr.leaf = i;
+                            placed = true;
+                        }
+                    } else if (sg.n_sphere < RTW_SS_SPHERES) {
+                        SmallSphere& sp = sg.sphere[sg.n_sphere++];
+                        sp.c = pk[2 * i];
+                        sp.prim_id = ids[i];
+                        sp.leaf = i;
+                        placed = true;
+                    }
+                }
+            }
+            if (!placed) {
+                key[i] = (xfi + 1) * 8 + kind;
+                order[n_left++] = i;
+            }
+        }
+        std::stable_sort(order, order + n_left, [&](int x, int y) { return key[x] < key[y]; });
+        ss.n_runs = 0;
+        for (int k = 0; k < n_left; k++) {
+            const int i = order[k];
+            ss.leaf[k].a = pk[2 * i];
+            ss.leaf[k].b = pk[2 * i + 1];
+            ss.leaf[k].ext = ext[i];
+            ss.leaf[k].prim_id = ids[i];
+            ss.leaf[k].leaf = i;
+            if (k == 0 || key[i] != key[order[k - 1]]) {
+                SmallRun& run = ss.run[ss.n_runs++];
+                run.first = k;
+                run.count = 0;
+                run.kind = key[i] & 7;
+                run.xf = (key[i] >> 3) - 1;
+            }
+            ss.run[ss.n_runs - 1].count++;
         }
         for (int j = 0; j < c->n_xforms; j++)
             for (int k = 0; k < 3; k++) ss.w2o[3 * j + k] = xf[6 * j + k];

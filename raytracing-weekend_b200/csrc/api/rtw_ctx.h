@@ -46,6 +46,7 @@ struct rtw_ctx {
     int opt_top_nodes = 1024;
     int opt_leaf_size = 0;
     int opt_small = -1;              // -1 = auto, 0 = never, 1 = whenever the scene qualifies
+    int opt_small_static = 1;        // small scenes: rects and spheres in the static table (layout.h SmallGroup)
     int opt_shade_ctas = 3;          // k_shade_all<kCtas>: 2, 3 or 4 resident CTAs per SM
     int opt_walker = -1;             // -1 = auto (rtw_build_accel), 0 = flat kernels, 1 = persistent walkers
     int opt_step_nodes = 16, opt_step_prims = 8, opt_min_active = 22;   // measured best on the Book-2 scene (tools/sweep_walk.sh)          // 0 = auto (rtw_build_accel), else 1..32

@@ -98,13 +98,51 @@ struct SmallLeaf {
     float4 a, b;                      // DScene::prims of the leaf
     float2 ext;                       // DScene::prim_ext
     int32_t prim_id;                  // DScene::leaf_prim
+    int32_t leaf;                     // index of this record in the scene's leaf order (what the hit record stores)
+};
+// The records are ordered by (transform, kind) and cut into RUNS of equal (transform, kind): the ray is
+// carried into a transform once per run and the inner loop of a run is ONE candidate test with no dispatch.
+// The order of the tests does not matter: the closest hit is the lexicographic minimum of (t, primitive id).
+struct SmallRun {
+    int32_t first, count;             // records [first, first + count) of SmallScene::leaf
+    int32_t kind;                     // RTW_PRIM_*
+    int32_t xf;                       // transform id, -1 = none (always -1 for moving spheres)
+};
+// The STATIC part of a small scene: rects and (non-moving) spheres sit in a table of fixed shape
+// [group][kind][slot], group = one transform (group 0 = untransformed).  The walk over it is fully
+// unrolled, so every record field is an immediate constant-bank operand of the instruction that uses
+// it (no index arithmetic, no load), and a run of an absent kind costs one uniform branch.
+// Records that do not fit the shape (other kinds, more than RTW_SS_* of a kind) stay in the runs.
+#define RTW_SS_GROUPS  3
+#define RTW_SS_RECTS   4      // per group and axis
+#define RTW_SS_SPHERES 2      // per group
+struct SmallRect {
+    float4 a;                         // bounds (lo, hi, lo, hi) of the two in-plane axes
+    float k;                          // plane offset
+    int32_t prim_id;
+    int32_t leaf;                     // index in the scene's leaf order
     int32_t pad;
 };
+struct SmallSphere {
+    float4 c;                         // centre, radius
+    int32_t prim_id, leaf, pad[2];
+};
+struct SmallGroup {
+    float4 w2o[3];                    // world→object rows (unused for group 0)
+    SmallRect rect[3][RTW_SS_RECTS];  // [axis: x, y, z]
+    SmallSphere sphere[RTW_SS_SPHERES];
+    int32_t n_rect[3];
+    int32_t n_sphere;
+};
 struct SmallScene {
-    SmallLeaf leaf[RTW_SMALL_MAX];
-    float4 w2o[3 * RTW_SMALL_MAX];    // world→object rows of transform j (first half of DScene::xforms)
-    int32_t n;                        // leaves
-    int32_t pad[3];
+    SmallGroup group[RTW_SS_GROUPS];
+    SmallLeaf leaf[RTW_SMALL_MAX];    // the records left to the runs
+    float4 w2o[3 * RTW_SMALL_MAX];    // world→object rows of transform j (first half of DScene::xforms), for the runs
+    SmallRun run[RTW_SMALL_MAX];
+    int32_t n;                        // leaves of the scene (static + runs)
+    int32_t n_runs;
+    int32_t n_groups;                 // groups in use (0 = nothing static)
+    int32_t pad;
 };
 
 // ---- wavefront state: structure of arrays over P path slots ---------------

@@ -177,52 +177,132 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
     return false;
 }
 
-// Small scenes (layout.h SmallScene): the one leaf range, leaf by leaf, with a warp-uniform
-// counter.  Same candidates, same lexicographic (t, primitive id) minimum as traverse_closest.
-RTW_HD bool small_closest(const SmallScene& ss, const RayW& r, float& t_best, uint32_t& leaf_best) {
-    const SrcSmall src{ss};
-    XfRay cur;
-    cur.xf = -1;
-    cur.o = r.o;
-    cur.d = r.d;
-    bool found = false;
-    float tb = r.tmax;
-    uint32_t lb = RTW_REF_NONE;
-    for (int leaf = 0; leaf < ss.n; leaf++) {
-        float t;
-        if (prim_candidate_uniform(src, (uint32_t)leaf, r, cur, t)) {
-            if (!found || t < tb) {
-                found = true;
-                tb = t;
-                lb = (uint32_t)leaf;
-            } else if (t == tb && ss.leaf[leaf].prim_id < ss.leaf[lb].prim_id) {
-                lb = (uint32_t)leaf;
-            }
-        }
+// Small scenes (layout.h SmallScene): the one leaf range as a static table plus runs.  Every counter
+// here is warp-uniform (it comes from the kernel-parameter copy of the scene): a group / run is "carry
+// the ray into its transform once, then one candidate test per record with no dispatch inside", and the
+// closest-hit update is selects only.  Same candidates, same lexicographic (t, primitive id) minimum as
+// traverse_closest; the order of the tests is free.
+struct SmallBest {
+    float tb;        // best t so far (r.tmax until something is found)
+    uint32_t leaf;   // scene leaf index of the best candidate, RTW_REF_NONE = none
+    int32_t pid;     // its primitive id (INT32_MAX until something is found: decides exact ties)
+};
+template <bool kAny>
+RTW_HD void small_accept(bool ok, float t, uint32_t leaf, int32_t pid, SmallBest& best, bool& any) {
+    if (kAny) {
+        any |= ok;
+    } else {
+        // a candidate has t <= r.tmax; with nothing found yet tb == r.tmax and pid == INT32_MAX, so t == tmax is taken
+        const bool take = ok & ((t < best.tb) | ((t == best.tb) & (pid < best.pid)));
+        best.tb = take ? t : best.tb;
+        best.leaf = take ? leaf : best.leaf;
+        best.pid = take ? pid : best.pid;
     }
-    t_best = tb;
-    leaf_best = lb;
+}
+// The static table, fully unrolled: g, axis and slot are compile-time constants.
+template <bool kAny, int kGroup>
+RTW_HD void small_group(const SmallScene& ss, const RayW& r, SmallBest& best, bool& any) {
+    const SmallGroup& g = ss.group[kGroup];
+    float3 o = r.o, d = r.d;
+    if (kGroup > 0) {
+        o = xform_point(g.w2o[0], g.w2o[1], g.w2o[2], r.o);
+        d = xform_vector(g.w2o[0], g.w2o[1], g.w2o[2], r.d);
+    }
+#pragma unroll
+    for (int j = 0; j < RTW_SS_RECTS; j++) {
+        if (j >= g.n_rect[0]) break;
+        float t;
+        const bool ok = rect_candidate(g.rect[0][j].a, g.rect[0][j].k, o.x, d.x, o.y, d.y, o.z, d.z, r.tmin, r.tmax, t);
+        small_accept<kAny>(ok, t, (uint32_t)g.rect[0][j].leaf, g.rect[0][j].prim_id, best, any);
+    }
+#pragma unroll
+    for (int j = 0; j < RTW_SS_RECTS; j++) {
+        if (j >= g.n_rect[1]) break;
+        float t;
+        const bool ok = rect_candidate(g.rect[1][j].a, g.rect[1][j].k, o.y, d.y, o.x, d.x, o.z, d.z, r.tmin, r.tmax, t);
+        small_accept<kAny>(ok, t, (uint32_t)g.rect[1][j].leaf, g.rect[1][j].prim_id, best, any);
+    }
+#pragma unroll
+    for (int j = 0; j < RTW_SS_RECTS; j++) {
+        if (j >= g.n_rect[2]) break;
+        float t;
+        const bool ok = rect_candidate(g.rect[2][j].a, g.rect[2][j].k, o.z, d.z, o.x, d.x, o.y, d.y, r.tmin, r.tmax, t);
+        small_accept<kAny>(ok, t, (uint32_t)g.rect[2][j].leaf, g.rect[2][j].prim_id, best, any);
+    }
+#pragma unroll
+    for (int j = 0; j < RTW_SS_SPHERES; j++) {
+        if (j >= g.n_sphere) break;
+        float t = 0.f;
+        const bool ok = sphere_candidate(f3(g.sphere[j].c), g.sphere[j].c.w, o, d, r.tmin, r.tmax, t);
+        small_accept<kAny>(ok, t, (uint32_t)g.sphere[j].leaf, g.sphere[j].prim_id, best, any);
+    }
+}
+// One run of the records that are not in the static table.
+template <bool kAny>
+RTW_HD void small_run(const SmallScene& ss, const SmallRun& run, const RayW& r, SmallBest& best, bool& any) {
+    const SrcSmall src{ss};
+    const uint32_t first = (uint32_t)run.first, end = (uint32_t)(run.first + run.count);
+    const int kind = run.kind;
+    float3 o = r.o, d = r.d;
+    if (run.xf >= 0) {
+        float4 r0, r1, r2;
+        src.w2o(run.xf, r0, r1, r2);
+        o = xform_point(r0, r1, r2, r.o);
+        d = xform_vector(r0, r1, r2, r.d);
+    }
+    // (unroll 1: an unrolled body makes the compiler index the constant bank per lane instead of
+    // through the uniform datapath)
+#pragma unroll 1
+    for (uint32_t i = first; i < end; i++) {
+        const float4 a = ss.leaf[i].a, b = ss.leaf[i].b;
+        float t = 0.f;
+        bool ok;
+        if (kind == RTW_PRIM_RECT_X) ok = rect_candidate(a, b.x, o.x, d.x, o.y, d.y, o.z, d.z, r.tmin, r.tmax, t);
+        else if (kind == RTW_PRIM_RECT_Y) ok = rect_candidate(a, b.x, o.y, d.y, o.x, d.x, o.z, d.z, r.tmin, r.tmax, t);
+        else if (kind == RTW_PRIM_RECT_Z) ok = rect_candidate(a, b.x, o.z, d.z, o.x, d.x, o.y, d.y, r.tmin, r.tmax, t);
+        else if (kind == RTW_PRIM_SPHERE) ok = sphere_candidate(f3(a), a.w, o, d, r.tmin, r.tmax, t);
+        else if (kind == RTW_PRIM_MOVING_SPHERE)
+            ok = sphere_candidate(moving_center(a, b, ss.leaf[i].ext, r.gather), a.w, r.o - motion_translation(a, b, r.time), r.d,
+                                  r.tmin, r.tmax, t);
+        else ok = medium_candidate(kind == RTW_PRIM_VOLUME_BOX, a, b, ss.leaf[i].prim_id, o, d, r, t);
+        small_accept<kAny>(ok, t, (uint32_t)ss.leaf[i].leaf, ss.leaf[i].prim_id, best, any);
+    }
+}
+template <bool kAny>
+RTW_HD bool small_walk(const SmallScene& ss, const RayW& r, SmallBest& best) {
+    best.tb = r.tmax;
+    best.leaf = RTW_REF_NONE;
+    best.pid = 0x7fffffff;
+    bool any = false;
+#if defined(__CUDA_ARCH__)
+#define RTW_SMALL_ALL_DONE() (kAny && __all_sync(0xffffffffu, any))
+#else
+#define RTW_SMALL_ALL_DONE() (kAny && any)
+#endif
+    // any hit: a lane that has its answer keeps walking (its result does not change any more) until
+    // every lane of the warp has one; the vote is taken once per group / run
+    if (0 < ss.n_groups) small_group<kAny, 0>(ss, r, best, any);
+    if (1 < ss.n_groups && !RTW_SMALL_ALL_DONE()) small_group<kAny, 1>(ss, r, best, any);
+    if (2 < ss.n_groups && !RTW_SMALL_ALL_DONE()) small_group<kAny, 2>(ss, r, best, any);
+    for (int ri = 0; ri < ss.n_runs; ri++) {
+        if (RTW_SMALL_ALL_DONE()) break;
+        small_run<kAny>(ss, ss.run[ri], r, best, any);
+    }
+#undef RTW_SMALL_ALL_DONE
+    return kAny ? any : best.leaf != RTW_REF_NONE;
+}
+// leaf_best: index in the scene's leaf order, as traverse_closest reports it
+RTW_HD bool small_closest(const SmallScene& ss, const RayW& r, float& t_best, uint32_t& leaf_best, int32_t* prim_best = nullptr) {
+    SmallBest best;
+    const bool found = small_walk<false>(ss, r, best);
+    t_best = best.tb;
+    leaf_best = best.leaf;
+    if (prim_best) *prim_best = found ? best.pid : -1;
     return found;
 }
-// Any hit.  The loop stays warp-uniform: a lane that has its answer keeps walking (its result is
-// not changed any more) until every lane of the warp has one.
 RTW_HD bool small_any(const SmallScene& ss, const RayW& r) {
-    const SrcSmall src{ss};
-    XfRay cur;
-    cur.xf = -1;
-    cur.o = r.o;
-    cur.d = r.d;
-    bool hit = false;
-    for (int leaf = 0; leaf < ss.n; leaf++) {
-        float t;
-        if (prim_candidate_uniform(src, (uint32_t)leaf, r, cur, t)) hit = true;
-#if defined(__CUDA_ARCH__)
-        if (__all_sync(0xffffffffu, hit)) break;
-#else
-        if (hit) break;
-#endif
-    }
-    return hit;
+    SmallBest best;
+    return small_walk<true>(ss, r, best);
 }
 
 }  // namespace rtw

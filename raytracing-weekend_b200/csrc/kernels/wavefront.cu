@@ -328,6 +328,9 @@ __global__ void __launch_bounds__(kBlock) k_traverse_small(const DScene sc, cons
             if (w.trace_use) slot = list[slot];
             alive = closest_ray_of(sc, w, slot, r);
         }
+        // a slot without a ray (drain tail of a frame) walks a harmless ray: the zero ray of a retired slot
+        // would send every division of its warp (k / 0) through the out-of-line slow path
+        if (!alive) { r.o = f3(0.f); r.d = f3(1.f); }
         // warp-uniform: a warp of empty slots walks nothing.  (Packing the live rays of a tile into fewer warps
         // was tried for the drain tail of a frame and is slower: one warp's walk is a ~1400-instruction
         // dependent chain, so a tile takes as long with one walking warp as with eight.)
@@ -353,7 +356,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const 
     for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const uint32_t i = tile * kBlock + threadIdx.x;
         RayW r;
-        r.o = f3(0.f); r.d = f3(0.f); r.tmin = 500 * 1.0e-7f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+        r.o = f3(0.f); r.d = f3(1.f); r.tmin = 500 * 1.0e-7f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         uint32_t slot = 0;
         const bool valid = i < n;
@@ -527,7 +530,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_small(const __grid_constant__ 
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
     RayW r;
-    r.o = f3(0.f); r.d = f3(0.f); r.tmin = 0.f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+    r.o = f3(0.f); r.d = f3(1.f); r.tmin = 0.f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
     if (valid) {
         const rtw_ray q = rays[i];
         r.o = f3(q.origin[0], q.origin[1], q.origin[2]);
@@ -537,11 +540,12 @@ __global__ void __launch_bounds__(kBlock) k_trace_small(const __grid_constant__ 
     if (hits) {
         float t;
         uint32_t leaf;
-        const bool found = small_closest(ss, r, t, leaf);
+        int32_t prim;
+        const bool found = small_closest(ss, r, t, leaf, &prim);
         if (valid) {
             rtw_hit h;
             h.t = found ? t : 0.f;
-            h.prim = found ? ss.leaf[leaf].prim_id : -1;
+            h.prim = prim;
             hits[i] = h;
         }
     }
