@@ -121,6 +121,9 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "shade_ctas")) {
         if (value < 2 || value > 4) return fail(c, RTW_ERR_INVALID, "shade_ctas out of range [2, 4]");
         c->opt_shade_ctas = (int)value;
+    } else if (!strcmp(name, "stream")) {
+        if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "stream out of range [-1, 1]");
+        c->opt_stream = (int)value;
     } else if (!strcmp(name, "profile")) {
         c->opt_profile = value ? 1 : 0;
     } else if (!strcmp(name, "lag")) {
@@ -487,6 +490,13 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
         c->cfg.step_nodes = 1; c->cfg.step_prims = RTW_MAX_LEAF_SIZE; c->cfg.min_active = 0;   // static mode
     }
     c->cfg.has_shadow = (sc.n_lights > 0 && sc.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN)));
+    // Streaming wavefront (kernels/stream.cu).  Measured on the B200 (tools/gpu_stream_scenes.sh): +26 % on the
+    // Book-1 scene (528 primitives, sky light, no NEE: 1398 -> 1763 Mpaths/s), where one LBVH walk per vertex
+    // rides in the shading kernel; slower where a vertex also traces a shadow ray through the LBVH (scenes 2, 4:
+    // two divergent walks at 2-3 CTAs per SM) and on the by-value small scenes (-5 %: the fused kernel is 170 KB
+    // of code against a 32 KB instruction cache).  Auto = LBVH scenes without an NEE stage, flat traversal.
+    c->cfg.stream = c->opt_stream >= 0 ? c->opt_stream != 0 : (!c->cfg.small && !c->cfg.has_shadow && !c->cfg.walker);
+    RTW_CUDA(c, stream_configure(sc, &c->cfg));
     c->accel_built = true;
     return RTW_OK;
 }

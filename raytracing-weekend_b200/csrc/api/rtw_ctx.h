@@ -30,6 +30,7 @@ struct rtw_ctx {
     std::vector<void*> wave_allocs;
     rtw::DWave wave{};
     int wave_capacity = 0;
+    bool wave_stream = false;           // what the pool was allocated for
     uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
     cudaEvent_t ring_events[8] = {};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
@@ -50,6 +51,7 @@ struct rtw_ctx {
     int opt_shade_ctas = 3;          // k_shade_all<kCtas>: 2, 3 or 4 resident CTAs per SM
     int opt_walker = -1;             // -1 = auto (rtw_build_accel), 0 = flat kernels, 1 = persistent walkers
     int opt_step_nodes = 16, opt_step_prims = 8, opt_min_active = 22;   // measured best on the Book-2 scene (tools/sweep_walk.sh)          // 0 = auto (rtw_build_accel), else 1..32
+    int opt_stream = -1;             // -1 = auto (rtw_build_accel), 0 = slot pool, 1 = streaming wavefront
     int opt_profile = 0;
     int opt_lag = 3;
 

@@ -9,7 +9,8 @@
 using namespace rtw;
 
 static int ensure_wave(rtw_ctx* c, int P) {
-    if (c->wave_capacity >= P) {
+    const bool stream = c->cfg.stream;
+    if (c->wave_capacity >= P && c->wave_stream == stream) {
         c->wave.P = P;
         return RTW_OK;
     }
@@ -18,16 +19,22 @@ static int ensure_wave(rtw_ctx* c, int P) {
     c->wave_capacity = 0;
     auto& pool = c->wave_allocs;
     DWave& w = c->wave;
-    RTW_CUDA(c, dalloc(pool, &w.rec, P));
-    RTW_CUDA(c, dalloc(pool, &w.hit, P));
-    RTW_CUDA(c, dalloc(pool, &w.rad, P));
-    RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_SLOTS * P));
-    RTW_CUDA(c, dalloc(pool, &w.sh_o, P));
-    RTW_CUDA(c, dalloc(pool, &w.sh_d, P));
-    RTW_CUDA(c, dalloc(pool, &w.sh_c, P));
+    w = DWave{};
+    if (stream) {   // 2 buffers x 4 classes x 5 float4 per path: any class may hold every path in flight
+        RTW_CUDA(c, dalloc(pool, &w.sq, (size_t)2 * 4 * 5 * P));
+    } else {
+        RTW_CUDA(c, dalloc(pool, &w.rec, P));
+        RTW_CUDA(c, dalloc(pool, &w.hit, P));
+        RTW_CUDA(c, dalloc(pool, &w.rad, P));
+        RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_SLOTS * P));
+        RTW_CUDA(c, dalloc(pool, &w.sh_o, P));
+        RTW_CUDA(c, dalloc(pool, &w.sh_d, P));
+        RTW_CUDA(c, dalloc(pool, &w.sh_c, P));
+    }
     RTW_CUDA(c, dalloc(pool, &w.counters, RTW_C_WORDS));
     w.P = P;
     c->wave_capacity = P;
+    c->wave_stream = stream;
     return RTW_OK;
 }
 
@@ -79,7 +86,9 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
         st.kernel_launches = launches;
         return RTW_OK;
     }
-    RTW_CUDA(c, wavefront_init(c->stream, w, &launches));
+    const bool stream = c->cfg.stream;
+    if (stream) RTW_CUDA(c, stream_init(c->stream, w, &launches));
+    else RTW_CUDA(c, wavefront_init(c->stream, w, &launches));
     const int lag = c->opt_lag;
     uint64_t iter = 0;
     bool done = (total == 0);
@@ -105,12 +114,13 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     w.trace_use = 0;
     while (!done) {
         w.parity = (int)(iter & 1);
-        w.trace_fill = (sparse && c->cfg.small) ? 1 : 0;
+        w.trace_fill = (sparse && c->cfg.small && !stream) ? 1 : 0;
         w.trace_use = (w.trace_fill && filled_prev) ? 1 : 0;
         filled_prev = w.trace_fill != 0;
         cudaEvent_t* sev = nullptr;
         if (c->opt_profile && sampled < kMaxSampled && iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
-        RTW_CUDA(c, wavefront_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
+        if (stream) RTW_CUDA(c, stream_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
+        else RTW_CUDA(c, wavefront_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
         uint32_t* snap = c->h_counters + (iter % 8) * RTW_C_WORDS;
         RTW_CUDA(c, cudaMemcpyAsync(snap, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, c->stream));
         RTW_CUDA(c, cudaEventRecord(c->ring_events[iter % 8], c->stream));

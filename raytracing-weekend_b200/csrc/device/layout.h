@@ -173,7 +173,12 @@ struct SmallScene {
 #define RTW_C_WORK_CLOSEST 16              // next pool slot to fetch (persistent traversal warps)
 #define RTW_C_WORK_SHADOW  17              // next shadow-queue entry to fetch
 #define RTW_C_TRACE0     18                // sparse mode: length of the trace list of even / odd iterations (two words)
-#define RTW_C_WORDS      20
+// streaming wavefront (device/stream.h): queue lengths [buffer][class], the paths the next fill starts,
+// the closest-hit rays the shading kernel traced this iteration
+#define RTW_C_SQ0        20                // 2 * 4 words
+#define RTW_C_NEW        28
+#define RTW_C_TRACED     29
+#define RTW_C_WORDS      32
 
 // Per-slot state is read and written through queue indices (a warp of the shading kernels holds
 // 32 arbitrary slots), so the records that are always used together are laid out as ONE 32-byte
@@ -203,6 +208,7 @@ struct DWave {
     float4* sh_o;       // shadow queue: origin.xyz, tmax
     float4* sh_d;       //               direction.xyz, slot bits
     float4* sh_c;       //               contribution.xyz, path seed bits
+    float4* sq;         // streaming wavefront: 2 buffers x 4 classes x 5 float4 arrays of P entries (device/stream.h)
     uint32_t* counters; // RTW_C_WORDS words
     float4* accum;      // Nx*Ny linear radiance sums (rgb) + sample count (w)
     int P;

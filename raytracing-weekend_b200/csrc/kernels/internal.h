@@ -57,6 +57,8 @@ struct LaunchCfg {
     int step_nodes, step_prims, min_active;   // persistent traversal: step bounds, refill threshold
     int shade_ctas;         // k_shade_all variant: resident CTAs per SM its registers are held to (2, 3 or 4)
     bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
+    bool stream;            // streaming wavefront (kernels/stream.cu) instead of the slot pool (kernels/wavefront.cu)
+    int grid_fill, grid_stream;   // its two grids
     const SmallScene* small; // host copy of a <= RTW_SMALL_MAX-leaf scene passed to the *_small kernels by value (else null)
 };
 cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
@@ -64,6 +66,11 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);
 cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
                                 uint64_t* launches, cudaEvent_t* stage_events /* 5 or null */);
 cudaError_t wavefront_init(cudaStream_t s, const DWave& w, uint64_t* launches);
+// Streaming wavefront (kernels/stream.cu): fill + trace, shade + shadow + trace, advance.
+cudaError_t stream_configure(const DScene& sc, LaunchCfg* cfg);
+cudaError_t stream_init(cudaStream_t s, const DWave& w, uint64_t* launches);
+cudaError_t stream_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
+                             uint64_t* launches, cudaEvent_t* stage_events /* 5 or null */);
 cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches);
 cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
 

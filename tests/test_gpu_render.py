@@ -56,6 +56,30 @@ def test_same_sample_images(director, orc, sid, Nx, Ny, spp):
     assert np.allclose(lin[..., :3], r, rtol=1e-5, atol=1e-6)
 
 
+@pytest.mark.parametrize("sid,Nx,Ny,spp", [(1, 96, 54, 16), (2, 64, 32, 16), (3, 48, 48, 32), (4, 64, 64, 16)])
+def test_streaming_wavefront_same_sample_images(director, orc, sid, Nx, Ny, spp):
+    """The streaming wavefront forced on every scene (LBVH walk inside the fused kernels on the large ones),
+    with a pool much smaller than the frame so that fills, drains and queue swaps all happen many times."""
+    director.init(Nx, Ny, spp)
+    director.set_option("stream", 1)
+    director.set_option("pool_paths", 4096)
+    try:
+        director.createScene(sid)
+        o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+        ref, c = o.render(Nx, Ny, spp, mode=1)
+        director.renderFrame(spp)
+        lin = director.linear()
+        st = director.stats()
+    finally:
+        director.set_option("stream", -1)
+        director.set_option("pool_paths", 0)
+    assert np.all(lin[..., 3] == spp)
+    r = ref[..., :3] / spp
+    assert relmse(lin[..., :3], r) <= RELMSE_SAME_SAMPLES
+    assert np.allclose(lin[..., :3], r, rtol=1e-5, atol=1e-6)
+    assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+
+
 def test_converged_image_relmse(director, orc):
     """Tier 2 of BASELINE.json: the GPU image at high spp against a CONVERGED reference image
     made by the oracle from DISJOINT samples (k = spp..2*spp-1), so agreement is statistical,
@@ -83,13 +107,20 @@ def test_pool_size_and_lag_do_not_change_the_image(director, orc):
     director.init(Nx, Ny, 8)
     director.createScene(0)
     imgs = []
-    for pool, lag in ((1024, 1), (4096, 3), (1 << 16, 7)):
-        director.set_option("pool_paths", pool)
-        director.set_option("lag", lag)
-        director.renderFrame(8)
-        imgs.append(director.linear())
-    director.set_option("pool_paths", 0)
-    director.set_option("lag", 3)
+    try:
+        for stream in (1, 0):
+            director.set_option("stream", stream)
+            director.createScene(0)
+            for pool, lag in ((1024, 1), (4096, 3), (1 << 16, 7)):
+                director.set_option("pool_paths", pool)
+                director.set_option("lag", lag)
+                director.renderFrame(8)
+                imgs.append(director.linear())
+                assert director.stats()["paths"] == Nx * Ny * 8 and np.all(imgs[-1][..., 3] == 8)
+    finally:
+        director.set_option("pool_paths", 0)
+        director.set_option("lag", 3)
+        director.set_option("stream", -1)
     for im in imgs[1:]:
         assert np.allclose(imgs[0], im, rtol=1e-5, atol=1e-6)   # fp32 atomic order only
 
@@ -154,18 +185,34 @@ def test_profile_option_reports_stage_times(director):
     st = director.stats()
     director.set_option("profile", 0)
     assert st["traverse_ms"] > 0 and st["shade_ms"] > 0 and st["logic_ms"] > 0
+    # the streaming wavefront reports fill (+ trace) as logic_ms, shade (+ shadow + trace) as shade_ms
+    director.set_option("profile", 1)
+    director.set_option("stream", 1)
+    try:
+        director.createScene(0)
+        director.renderFrame(2)
+        st = director.stats()
+    finally:
+        director.set_option("profile", 0)
+        director.set_option("stream", -1)
+    assert st["shade_ms"] > 0 and st["logic_ms"] > 0
 
 
 @pytest.mark.parametrize("sid,Nx,Ny", [(0, 64, 64), (3, 48, 48), (1, 96, 54), (4, 64, 64)])
 def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
-    """Flat per-thread traversal kernels vs the by-value small-scene kernels (scenes of <= 16
-    primitives; the option is ignored elsewhere) vs persistent walkers with dynamic ray fetching, and
-    several step / refill settings: the 1 spp image stays bit-exact (closest hit is the minimum
-    of (t, primitive id), independent of the order rays and nodes are visited in)."""
+    """Slot-pool wavefront (flat per-thread traversal kernels vs the by-value small-scene kernels — scenes
+    of <= 16 primitives; the option is ignored elsewhere — vs persistent walkers with dynamic ray
+    fetching, several step / refill settings) vs the streaming wavefront (kernels/stream.cu, by-value
+    small-scene walk or the LBVH): the 1 spp image stays bit-exact (closest hit is the minimum of
+    (t, primitive id), independent of the order rays and nodes are visited in; a sample is the same
+    random walk wherever its state lives)."""
     director.init(Nx, Ny, 1)
     ref = None
     try:
-        for opts in ({"walker": 0, "small": 0}, {"walker": 0, "small": 1}, {"walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
+        for opts in ({"stream": 0, "walker": 0, "small": 0}, {"stream": 0, "walker": 0, "small": 1},
+                     {"stream": 1, "walker": 0, "small": 1}, {"stream": 1, "walker": 0, "small": 0},
+                     {"stream": 1, "walker": 0, "small": 0, "shade_ctas": 2}, {"stream": 1, "walker": 0, "small": 1, "shade_ctas": 4},
+                     {"stream": 0, "shade_ctas": 3, "walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
                      {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1}):
             for k, v in opts.items():
                 director.set_option(k, v)
@@ -181,5 +228,5 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             rh, _ = o.trace_closest(director.camera_rays(0), 1)
             assert np.array_equal(hits, rh)
     finally:
-        for k, v in {"walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
+        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
             director.set_option(k, v)
