@@ -304,6 +304,18 @@ const rtw_scene_desc* rtw_scene_get_desc(const rtw_scene* s);
 const char* rtw_scene_description(const rtw_scene* s);
 void rtw_scene_free(rtw_scene* s);
 
+/* ---- scene wire format (the step before the path: the reference's scenes are C++
+ *      functions, scene/ioScene.h:180-982; here a flattened scene is a file) ------
+ * rtw_scene_save writes `desc` (+ an optional description text) as one little-endian
+ * file: magic "RTWS", version, header, the PODs above array by array, FNV-1a
+ * checksum.  rtw_scene_load reads it back into an rtw_scene (free it with
+ * rtw_scene_free) after validating sizes, checksum and every index a kernel follows.
+ * RTW_ERR_IO: cannot open / short file; RTW_ERR_INVALID: not a scene file, wrong
+ * version, checksum mismatch, index out of range.  rtw_scene_io_error(): the reason. */
+int  rtw_scene_save(const rtw_scene_desc* desc, const char* description, const char* path);
+int  rtw_scene_load(const char* path, rtw_scene** out);
+const char* rtw_scene_io_error(void);
+
 /* ---- output (replaces Director::printPPM, Director.cpp:1010-1031) ------ */
 /* P3 text, top row first, int(255.99f*clamp(c,0,1)); path NULL or "-" → stdout. */
 int  rtw_write_ppm(const char* path, int Nx, int Ny, const float* rgba);

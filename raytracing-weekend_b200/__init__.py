@@ -16,7 +16,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "librtw.so")
+LIB_PATH = os.environ.get("RTW_LIB") or os.path.join(_HERE, "librtw.so")   # RTW_LIB: tuning builds only
 ASSET_DIR = os.path.join(REPO_ROOT, "assets")
 
 RTW_OK, RTW_ERR_INVALID, RTW_ERR_CUDA, RTW_ERR_NO_DEVICE, RTW_ERR_STATE, RTW_ERR_IO = range(6)
@@ -115,7 +115,7 @@ ABI_SYMBOLS = [
     "rtw_build_accel", "rtw_render", "rtw_render_accum", "rtw_tonemap", "rtw_get_linear", "rtw_set_option",
     "rtw_get_stats", "rtw_trace_closest", "rtw_trace_any", "rtw_rng_stream", "rtw_camera_rays", "rtw_bvh_info_get",
     "rtw_bvh_download", "rtw_sort_pairs", "rtw_scene_create", "rtw_scene_get_desc", "rtw_scene_description",
-    "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval",
+    "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval", "rtw_scene_save", "rtw_scene_load", "rtw_scene_io_error",
 ]
 
 _lib = None
@@ -162,6 +162,9 @@ def lib():
         "rtw_scene_get_desc": (C.POINTER(SceneDesc), [vp]),
         "rtw_scene_description": (C.c_char_p, [vp]),
         "rtw_scene_free": (None, [vp]),
+        "rtw_scene_save": (i32, [vp, C.c_char_p, C.c_char_p]),
+        "rtw_scene_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "rtw_scene_io_error": (C.c_char_p, []),
         "rtw_write_ppm": (i32, [C.c_char_p, i32, i32, vp]),
     }
     for name, (res, args) in sig.items():
@@ -187,6 +190,22 @@ class Scene:
         if rc != RTW_OK:
             raise RtwError("rtw_scene_create(%d) failed: %d" % (scene_id, rc))
         self.scene_id, self.Nx, self.Ny = scene_id, Nx, Ny
+
+    @classmethod
+    def load(cls, path, Nx=0, Ny=0):
+        """Scene wire format (rtw_scene_load): a flattened scene read back from a file."""
+        self = cls.__new__(cls)
+        self._h = C.c_void_p()
+        rc = lib().rtw_scene_load(str(path).encode(), C.byref(self._h))
+        if rc != RTW_OK:
+            raise RtwError("rtw_scene_load(%s) failed: %d (%s)" % (path, rc, lib().rtw_scene_io_error().decode()))
+        self.scene_id, self.Nx, self.Ny = -1, Nx, Ny
+        return self
+
+    def save(self, path):
+        rc = lib().rtw_scene_save(C.cast(self.desc, C.c_void_p), self.description.encode(), str(path).encode())
+        if rc != RTW_OK:
+            raise RtwError("rtw_scene_save(%s) failed: %d (%s)" % (path, rc, lib().rtw_scene_io_error().decode()))
 
     @property
     def desc(self):
@@ -236,6 +255,11 @@ class Director:
     # Director::createScene(n)
     def createScene(self, scene_number, asset_dir=None, n_stress_prims=0):
         self.scene = Scene(scene_number, self.Nx, self.Ny, asset_dir, n_stress_prims)
+        self.upload(self.scene.desc)
+
+    def loadScene(self, path):
+        """createScene from a scene file (rtw_scene_load) instead of one of the built-in scene functions."""
+        self.scene = Scene.load(path, self.Nx, self.Ny)
         self.upload(self.scene.desc)
 
     def upload(self, desc_ptr):

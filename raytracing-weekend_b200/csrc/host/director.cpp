@@ -29,6 +29,25 @@ void Director::createScene(unsigned int sceneNumber) {
     if (_verbose) std::cerr << "INFO: Scene description: " << rtw_scene_description(m_scene) << std::endl;  // Director.cpp:965-968
 }
 
+void Director::createSceneFromFile(const char* path) {
+    int rc = rtw_scene_load(path, &m_scene);
+    if (rc != RTW_OK) {
+        std::cerr << "ERROR: cannot load scene " << path << ": " << rtw_scene_io_error() << std::endl;
+        std::exit(EXIT_FAILURE);
+    }
+    check(rtw_upload_scene(m_ctx, rtw_scene_get_desc(m_scene)), "rtw_upload_scene");
+    check(rtw_build_accel(m_ctx), "rtw_build_accel");
+    if (_verbose) std::cerr << "INFO: Scene description: " << rtw_scene_description(m_scene) << std::endl;
+}
+
+void Director::saveScene(const char* path) {
+    int rc = rtw_scene_save(rtw_scene_get_desc(m_scene), rtw_scene_description(m_scene), path);
+    if (rc != RTW_OK) {
+        std::cerr << "ERROR: cannot save scene " << path << ": " << rtw_scene_io_error() << std::endl;
+        std::exit(EXIT_FAILURE);
+    }
+}
+
 void Director::renderFrame() {
     m_frame.assign((size_t)m_Nx * m_Ny * 4, 0.f);
     check(rtw_render(m_ctx, m_Nx, m_Ny, m_Ns, m_maxRayDepth, m_frame.data()), "rtw_render");

@@ -13,6 +13,8 @@ public:
 
     void init(unsigned int width, unsigned int height, unsigned int samples);   // Director.cpp:33
     void createScene(unsigned int sceneNumber);                                  // Director.cpp:951
+    void createSceneFromFile(const char* path);    // scene wire format (rtw_scene_load) instead of a built-in scene function
+    void saveScene(const char* path);              // rtw_scene_save of the scene in use
     void renderFrame();                                                          // Director.cpp:971
     void printPPM(const char* path = "-");                                       // Director.cpp:1010
     void destroy();                                                              // Director.cpp:86

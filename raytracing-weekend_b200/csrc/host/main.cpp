@@ -52,6 +52,8 @@ int main(int argc, char* argv[]) {
     -d N           CUDA device index (default 0).
     -a DIR         Asset directory holding earthmap.ppm (default "assets").
     -j             Print one JSON line with render statistics on stderr.
+    -f FILE        Render the scene stored in FILE (scene wire format) instead of scene -s N.
+    -w FILE        Write the scene in use to FILE (scene wire format).
 
 )";
         return EXIT_SUCCESS;
@@ -117,6 +119,8 @@ int main(int argc, char* argv[]) {
     if (!dev.empty()) parse_int(dev, device);
     const std::string& out = cl_input.getCmdOption("-o");
     const std::string& assets = cl_input.getCmdOption("-a");
+    const std::string& scene_in = cl_input.getCmdOption("-f");
+    const std::string& scene_out = cl_input.getCmdOption("-w");
 
     Director director(Qverbose, Qdebug);
     director.setDevice(device);
@@ -129,7 +133,9 @@ int main(int argc, char* argv[]) {
         std::cerr << "INFO: Number of rays sent per pixel: " << Ns << std::endl;
         std::cerr << "INFO: Scene number selected: " << Nscene << std::endl;
     }
-    director.createScene(Nscene);
+    if (!scene_in.empty()) director.createSceneFromFile(scene_in.c_str());
+    else director.createScene(Nscene);
+    if (!scene_out.empty()) director.saveScene(scene_out.c_str());
     director.renderFrame();
     auto stop = std::chrono::system_clock::now();
     auto time_seconds = std::chrono::duration<float>(stop - start).count();

@@ -616,6 +616,221 @@ extern "C" const rtw_scene_desc* rtw_scene_get_desc(const rtw_scene* s) { return
 extern "C" const char* rtw_scene_description(const rtw_scene* s) { return s ? s->description.c_str() : ""; }
 extern "C" void rtw_scene_free(rtw_scene* s) { delete s; }
 
+// ---- scene wire format (the step BEFORE the path) ---------------------------
+// The reference has no scene file: its five scenes are C++ functions (scene/ioScene.h:180-982) that
+// fill OptiX records.  Here a flattened scene (rtw_scene_desc) is data: one little-endian file,
+//   u32 magic "RTWS", u32 version, u32 header bytes, then the header
+//   { i32 n_prims, n_transforms, n_materials, n_textures, n_perlin, n_images, n_lights, has_light_rect,
+//     sky_light, reserved; rtw_light_rect; rtw_camera; u32 description bytes },
+//   the description text, the arrays in that order as their C-ABI PODs (include/rtw.h) — every image as
+//   { i32 width, height } + RGBA8 texels —, and a u64 FNV-1a checksum of everything before it.
+// rtw_scene_load validates counts, sizes, the checksum and every index a kernel would follow, so a file
+// that loads cannot send the device out of bounds.
+namespace {
+
+constexpr uint32_t kSceneMagic = 0x53575452u;   // "RTWS"
+constexpr uint32_t kSceneVersion = 1u;
+
+struct SceneFileHeader {
+    int32_t n_prims, n_transforms, n_materials, n_textures, n_perlin, n_images, n_lights, has_light_rect;
+    int32_t sky_light, reserved;
+    rtw_light_rect light_rect;
+    rtw_camera camera;
+    uint32_t description_bytes;
+};
+
+struct Fnv {
+    uint64_t h = 1469598103934665603ull;
+    void add(const void* p, size_t n) {
+        const uint8_t* b = static_cast<const uint8_t*>(p);
+        for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    }
+};
+
+struct SceneWriter {
+    FILE* f;
+    Fnv sum;
+    bool ok = true;
+    void put(const void* p, size_t n) {
+        if (n == 0) return;
+        if (fwrite(p, 1, n, f) != n) ok = false;
+        sum.add(p, n);
+    }
+};
+
+struct SceneReader {
+    FILE* f;
+    Fnv sum;
+    bool ok = true;
+    void get(void* p, size_t n) {
+        if (n == 0) return;
+        if (!ok || fread(p, 1, n, f) != n) { ok = false; memset(p, 0, n); return; }
+        sum.add(p, n);
+    }
+};
+
+bool index_ok(int32_t i, int32_t n, bool may_be_none) { return (may_be_none && i == -1) || (i >= 0 && i < n); }
+
+// every index and enumeration a kernel follows
+const char* validate_desc(const rtw_scene_desc& d) {
+    if (d.n_prims < 1 || d.n_prims > (1 << 25)) return "primitive count out of range [1, 2^25]";
+    if (d.n_materials < 1) return "no materials";
+    if (d.n_lights > 8) return "more than 8 lights";
+    for (int i = 0; i < d.n_prims; i++) {
+        const rtw_prim& p = d.prims[i];
+        if (p.type < 0 || p.type >= RTW_PRIM_TYPE_COUNT) return "primitive type out of range";
+        if (!index_ok(p.material, d.n_materials, false)) return "primitive material index out of range";
+        if (!index_ok(p.transform, d.n_transforms, true)) return "primitive transform index out of range";
+    }
+    for (int i = 0; i < d.n_materials; i++) {
+        const rtw_material& m = d.materials[i];
+        if (m.type < 0 || m.type >= RTW_MAT_TYPE_COUNT) return "material type out of range";
+        if (!index_ok(m.texture, d.n_textures, true)) return "material texture index out of range";
+        const bool textured = m.type == RTW_MAT_LAMBERTIAN || m.type == RTW_MAT_DIFFUSE_LIGHT || m.type == RTW_MAT_METAL ||
+                              m.type == RTW_MAT_ISOTROPIC;
+        if (textured && m.texture < 0) return "textured material without a texture";
+    }
+    for (int i = 0; i < d.n_textures; i++) {
+        const rtw_texture& t = d.textures[i];
+        if (t.type < 0 || t.type >= RTW_TEX_TYPE_COUNT) return "texture type out of range";
+        if (t.type == RTW_TEX_CHECKER && (!index_ok(t.odd, d.n_textures, false) || !index_ok(t.even, d.n_textures, false)))
+            return "checker child index out of range";
+        if (t.type == RTW_TEX_CHECKER && (d.textures[t.odd].type == RTW_TEX_CHECKER || d.textures[t.even].type == RTW_TEX_CHECKER))
+            return "nested checker textures";
+        if (t.type == RTW_TEX_NOISE && !index_ok(t.perlin, d.n_perlin, false)) return "noise table index out of range";
+        if (t.type == RTW_TEX_IMAGE && !index_ok(t.image, d.n_images, false)) return "image index out of range";
+    }
+    for (int i = 0; i < d.n_perlin; i++)
+        for (int k = 0; k < 256; k++) {
+            const rtw_perlin& p = d.perlin[i];
+            if ((p.perm_x[k] | p.perm_y[k] | p.perm_z[k]) & ~255) return "Perlin permutation entry out of range";
+        }
+    for (int i = 0; i < d.n_images; i++)
+        if (d.images[i].width < 1 || d.images[i].height < 1 || !d.images[i].rgba) return "empty image";
+    if (d.has_light_rect && (d.light_rect.axis < 0 || d.light_rect.axis > 2)) return "light rectangle axis out of range";
+    return nullptr;
+}
+
+}  // namespace
+
+static std::string g_scene_io_error;
+extern "C" const char* rtw_scene_io_error(void) { return g_scene_io_error.c_str(); }
+
+extern "C" int rtw_scene_save(const rtw_scene_desc* d, const char* description, const char* path) {
+    if (!d || !path) return RTW_ERR_INVALID;
+    if (const char* why = validate_desc(*d)) {
+        g_scene_io_error = why;
+        return RTW_ERR_INVALID;
+    }
+    FILE* f = fopen(path, "wb");
+    if (!f) {
+        g_scene_io_error = std::string("cannot open ") + path;
+        return RTW_ERR_IO;
+    }
+    SceneWriter w{f};
+    const std::string text = description ? description : "";
+    SceneFileHeader h{};
+    h.n_prims = d->n_prims; h.n_transforms = d->n_transforms; h.n_materials = d->n_materials;
+    h.n_textures = d->n_textures; h.n_perlin = d->n_perlin; h.n_images = d->n_images; h.n_lights = d->n_lights;
+    h.has_light_rect = d->has_light_rect; h.sky_light = d->sky_light; h.reserved = 0;
+    h.light_rect = d->light_rect;
+    h.camera = d->camera;
+    h.description_bytes = (uint32_t)text.size();
+    const uint32_t pre[3] = {kSceneMagic, kSceneVersion, (uint32_t)sizeof(SceneFileHeader)};
+    w.put(pre, sizeof(pre));
+    w.put(&h, sizeof(h));
+    w.put(text.data(), text.size());
+    w.put(d->prims, sizeof(rtw_prim) * (size_t)d->n_prims);
+    w.put(d->transforms, sizeof(rtw_transform) * (size_t)d->n_transforms);
+    w.put(d->materials, sizeof(rtw_material) * (size_t)d->n_materials);
+    w.put(d->textures, sizeof(rtw_texture) * (size_t)d->n_textures);
+    w.put(d->perlin, sizeof(rtw_perlin) * (size_t)d->n_perlin);
+    for (int i = 0; i < d->n_images; i++) {
+        const int32_t wh[2] = {d->images[i].width, d->images[i].height};
+        w.put(wh, sizeof(wh));
+        w.put(d->images[i].rgba, (size_t)wh[0] * (size_t)wh[1] * 4);
+    }
+    w.put(d->lights, sizeof(rtw_light) * (size_t)d->n_lights);
+    const uint64_t sum = w.sum.h;
+    if (fwrite(&sum, 1, sizeof(sum), f) != sizeof(sum)) w.ok = false;
+    if (fclose(f) != 0) w.ok = false;
+    if (!w.ok) {
+        g_scene_io_error = std::string("short write to ") + path;
+        return RTW_ERR_IO;
+    }
+    return RTW_OK;
+}
+
+extern "C" int rtw_scene_load(const char* path, rtw_scene** out) {
+    if (!path || !out) return RTW_ERR_INVALID;
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) {
+        g_scene_io_error = std::string("cannot open ") + path;
+        return RTW_ERR_IO;
+    }
+    fseek(f, 0, SEEK_END);
+    const long file_bytes = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    SceneReader r{f};
+    rtw_scene* s = new rtw_scene();
+    auto bad = [&](int code, const std::string& why) {
+        g_scene_io_error = why;
+        fclose(f);
+        delete s;
+        return code;
+    };
+    uint32_t pre[3];
+    r.get(pre, sizeof(pre));
+    if (!r.ok || pre[0] != kSceneMagic) return bad(RTW_ERR_INVALID, "not an RTWS scene file");
+    if (pre[1] != kSceneVersion || pre[2] != sizeof(SceneFileHeader)) return bad(RTW_ERR_INVALID, "unsupported scene file version");
+    SceneFileHeader h;
+    r.get(&h, sizeof(h));
+    if (!r.ok) return bad(RTW_ERR_IO, "truncated scene file (header)");
+    const int32_t counts[7] = {h.n_prims, h.n_transforms, h.n_materials, h.n_textures, h.n_perlin, h.n_images, h.n_lights};
+    for (int32_t n : counts)
+        if (n < 0 || n > (1 << 25)) return bad(RTW_ERR_INVALID, "array count out of range");
+    // the arrays must fit in what is left of the file (a count cannot make us allocate more than the file holds)
+    const unsigned long long need = (unsigned long long)h.description_bytes + sizeof(rtw_prim) * (unsigned long long)h.n_prims +
+        sizeof(rtw_transform) * (unsigned long long)h.n_transforms + sizeof(rtw_material) * (unsigned long long)h.n_materials +
+        sizeof(rtw_texture) * (unsigned long long)h.n_textures + sizeof(rtw_perlin) * (unsigned long long)h.n_perlin +
+        8ull * (unsigned long long)h.n_images + sizeof(rtw_light) * (unsigned long long)h.n_lights + 8ull;
+    if (file_bytes < 0 || need + sizeof(pre) + sizeof(h) > (unsigned long long)file_bytes) return bad(RTW_ERR_IO, "truncated scene file");
+    s->description.resize(h.description_bytes);
+    r.get(&s->description[0], h.description_bytes);
+    s->prims.resize(h.n_prims);       r.get(s->prims.data(), sizeof(rtw_prim) * s->prims.size());
+    s->xforms.resize(h.n_transforms); r.get(s->xforms.data(), sizeof(rtw_transform) * s->xforms.size());
+    s->mats.resize(h.n_materials);    r.get(s->mats.data(), sizeof(rtw_material) * s->mats.size());
+    s->texs.resize(h.n_textures);     r.get(s->texs.data(), sizeof(rtw_texture) * s->texs.size());
+    s->perlin.resize(h.n_perlin);     r.get(s->perlin.data(), sizeof(rtw_perlin) * s->perlin.size());
+    for (int i = 0; i < h.n_images && r.ok; i++) {
+        int32_t wh[2] = {0, 0};
+        r.get(wh, sizeof(wh));
+        if (!r.ok || wh[0] < 1 || wh[1] < 1 || (unsigned long long)wh[0] * (unsigned long long)wh[1] * 4ull > (unsigned long long)file_bytes)
+            return bad(RTW_ERR_INVALID, "bad image size");
+        rtw_image im{};
+        im.width = wh[0];
+        im.height = wh[1];
+        s->images.push_back(im);
+        s->image_data.emplace_back((size_t)wh[0] * (size_t)wh[1] * 4);
+        r.get(s->image_data.back().data(), s->image_data.back().size());
+    }
+    s->lights.resize(h.n_lights);     r.get(s->lights.data(), sizeof(rtw_light) * s->lights.size());
+    if (!r.ok) return bad(RTW_ERR_IO, "truncated scene file");
+    uint64_t sum = 0;
+    if (fread(&sum, 1, sizeof(sum), f) != sizeof(sum)) return bad(RTW_ERR_IO, "truncated scene file (checksum)");
+    if (sum != r.sum.h) return bad(RTW_ERR_INVALID, "scene file checksum mismatch");
+    s->desc.has_light_rect = h.has_light_rect;
+    s->desc.light_rect = h.light_rect;
+    s->desc.camera = h.camera;
+    s->finish();
+    s->desc.sky_light = h.sky_light;
+    if (const char* why = validate_desc(s->desc)) return bad(RTW_ERR_INVALID, why);
+    fclose(f);
+    *out = s;
+    return RTW_OK;
+}
+
 // Director::printPPM, Director.cpp:1010-1031 (source buffer is the un-denoised frame, Q30)
 extern "C" int rtw_write_ppm(const char* path, int Nx, int Ny, const float* rgba) {
     if (!rgba || Nx <= 0 || Ny <= 0) return RTW_ERR_INVALID;
