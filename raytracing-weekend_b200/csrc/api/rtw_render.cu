@@ -53,9 +53,11 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     const unsigned long long npix = (unsigned long long)Nx * (unsigned long long)Ny;
     if (npix > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image too large");
     const unsigned long long total = npix * (unsigned long long)sample_count;
-    // Pool size: 2^21 slots, 2^22 for long frames (>= 2^28 paths: measured +2.7 % on C2 at 1024 spp; on shorter
-    // frames the longer fill/drain tail of the bigger pool costs more than it gains).  Option pool_paths overrides.
-    long long P = c->opt_pool_paths > 0 ? c->opt_pool_paths : (total >= (1ull << 28) ? (1ll << 22) : (1ll << 21));
+    // Pool size (measured on the B200, tools/diag_tail.py, C2 at 32-1024 spp): 2^22 slots is the fastest at every
+    // frame length from 64 spp (23 M paths) up — 18.9 ms against 19.8 ms with 2^21 at 128 spp, the share one GPU
+    // of eight renders — while 2^24 slots lose 28 % (the gathers through the queues then span 2.7 GB).
+    // Option pool_paths overrides.
+    long long P = c->opt_pool_paths > 0 ? c->opt_pool_paths : (total >= (1ull << 23) ? (1ll << 22) : (1ll << 21));
     if ((unsigned long long)P > total) P = (long long)std::max<unsigned long long>(total, 1024ull);
     P = (P + 255) / 256 * 256;
     int rc = ensure_wave(c, (int)P);

@@ -7,9 +7,9 @@ d = rtw.Director(0)
 d.init(600, 600, 128)
 d.createScene(0)
 d.set_option("profile", 1)
-for pool in (1 << 21,):
+for pool in (1 << 22, 1 << 23, 1 << 24):
     d.set_option("pool_paths", pool)
-    for spp in (32, 64, 128, 256):
+    for spp in (32, 128, 512, 1024):
         for rep in range(3):
             t0 = time.perf_counter()
             d.renderFrame(spp)
