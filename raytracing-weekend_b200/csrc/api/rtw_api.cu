@@ -57,8 +57,6 @@ extern "C" int rtw_create(int device, rtw_ctx** out) {
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_end);
-    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ring_events[i], cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&c->h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8);
     if (e != cudaSuccess) {
         g_create_error = std::string("context setup: ") + cudaGetErrorString(e);
         delete c;
@@ -81,10 +79,15 @@ extern "C" int rtw_destroy(rtw_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     dfree_all(c->scene_allocs);
-    dfree_all(c->wave_allocs);
+    for (auto& wv : c->waves) {
+        if (wv.stream) cudaStreamSynchronize(wv.stream);
+        dfree_all(wv.allocs);
+        if (wv.h_counters) cudaFreeHost(wv.h_counters);
+        for (auto& e : wv.ring_events) if (e) cudaEventDestroy(e);
+        if (wv.ev_done) cudaEventDestroy(wv.ev_done);
+        if (wv.stream && wv.stream != c->stream) cudaStreamDestroy(wv.stream);
+    }
     free_frame(c);
-    if (c->h_counters) cudaFreeHost(c->h_counters);
-    for (auto& e : c->ring_events) if (e) cudaEventDestroy(e);
     for (auto& e : c->prof_events) if (e) cudaEventDestroy(e);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -124,6 +127,12 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "stream")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "stream out of range [-1, 1]");
         c->opt_stream = (int)value;
+    } else if (!strcmp(name, "grid_pct")) {
+        if (value < 1 || value > 100) return fail(c, RTW_ERR_INVALID, "grid_pct out of range [1, 100]");
+        c->opt_grid_pct = (int)value;
+    } else if (!strcmp(name, "waves")) {
+        if (value < 0 || value > rtw_ctx::kMaxWaves) return fail(c, RTW_ERR_INVALID, "waves out of range [0, 4] (0 = auto)");
+        c->opt_waves = (int)value;
     } else if (!strcmp(name, "profile")) {
         c->opt_profile = value ? 1 : 0;
     } else if (!strcmp(name, "lag")) {
@@ -484,6 +493,12 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
         c->cfg.small = &c->small;
     }
     RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
+    if (c->opt_grid_pct < 100) {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+        auto share = [&](int& g) { g = std::max(sms, (g * c->opt_grid_pct / 100 + sms / 2) / sms * sms); };
+        share(c->cfg.grid_logic); share(c->cfg.grid_traverse); share(c->cfg.grid_shade); share(c->cfg.grid_shadow);
+    }
     c->cfg.class_mask = c->class_mask;
     c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;
     if (sc.root & RTW_REF_LEAF) {   // one leaf range: every ray does the same walk, nothing to rebalance

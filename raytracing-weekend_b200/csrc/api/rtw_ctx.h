@@ -26,15 +26,25 @@ struct rtw_ctx {
     int leaf_size = 1;
     float scene_min[3] = {0, 0, 0}, scene_max[3] = {0, 0, 0};
 
-    // ---- wavefront pool ----
-    std::vector<void*> wave_allocs;
-    rtw::DWave wave{};
-    int wave_capacity = 0;
-    bool wave_stream = false;           // what the pool was allocated for
-    uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
-    cudaEvent_t ring_events[8] = {};
+    // ---- wavefront pools ----
+    // A frame is rendered by `n_waves` independent pools ("waves"), each with its own stream, its own share of
+    // the samples (sample k of a pixel goes to wave k mod n_waves) and its own counters; their kernels run
+    // concurrently, so an instruction-bound traversal launch of one wave overlaps a DRAM-bound shading launch
+    // of another (rtw_render.cu).  Wave 0 uses `stream`.
+    static constexpr int kMaxWaves = 4;
+    struct Wave {
+        std::vector<void*> allocs;
+        rtw::DWave w{};
+        int capacity = 0;
+        bool for_stream = false;            // what the pool was allocated for (streaming wavefront or slot pool)
+        cudaStream_t stream = nullptr;
+        uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
+        cudaEvent_t ring_events[8] = {};
+        cudaEvent_t ev_done = nullptr;
+    };
+    Wave waves[kMaxWaves];
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    std::vector<cudaEvent_t> prof_events;  // 5 per sampled iteration (profile option)
+    std::vector<cudaEvent_t> prof_events;  // 5 per sampled iteration (profile option; wave 0)
 
     // ---- last frame ----
     float4* d_accum = nullptr;          // linear sums of the last rtw_render
@@ -52,6 +62,8 @@ struct rtw_ctx {
     int opt_walker = -1;             // -1 = auto (rtw_build_accel), 0 = flat kernels, 1 = persistent walkers
     int opt_step_nodes = 16, opt_step_prims = 8, opt_min_active = 22;   // measured best on the Book-2 scene (tools/sweep_walk.sh)          // 0 = auto (rtw_build_accel), else 1..32
     int opt_stream = -1;             // -1 = auto (rtw_build_accel), 0 = slot pool, 1 = streaming wavefront
+    int opt_grid_pct = 100;          // share of the resident-CTA grids one context launches (two contexts on one GPU: 50)
+    int opt_waves = 0;               // 0 = auto (rtw_render.cu), else 1..4 concurrent pools per frame
     int opt_profile = 0;
     int opt_lag = 3;
 

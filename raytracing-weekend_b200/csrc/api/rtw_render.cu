@@ -8,17 +8,25 @@
 
 using namespace rtw;
 
-static int ensure_wave(rtw_ctx* c, int P) {
+static int ensure_wave(rtw_ctx* c, int j, int P) {
+    rtw_ctx::Wave& wv = c->waves[j];
     const bool stream = c->cfg.stream;
-    if (c->wave_capacity >= P && c->wave_stream == stream) {
-        c->wave.P = P;
+    if (!wv.stream) {
+        if (j == 0) wv.stream = c->stream;
+        else RTW_CUDA(c, cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
+        for (auto& e : wv.ring_events) RTW_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        RTW_CUDA(c, cudaEventCreateWithFlags(&wv.ev_done, cudaEventDisableTiming));
+        RTW_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&wv.h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8));
+    }
+    if (wv.capacity >= P && wv.for_stream == stream) {
+        wv.w.P = P;
         return RTW_OK;
     }
-    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
-    dfree_all(c->wave_allocs);
-    c->wave_capacity = 0;
-    auto& pool = c->wave_allocs;
-    DWave& w = c->wave;
+    RTW_CUDA(c, cudaStreamSynchronize(wv.stream));
+    dfree_all(wv.allocs);
+    wv.capacity = 0;
+    auto& pool = wv.allocs;
+    DWave& w = wv.w;
     w = DWave{};
     if (stream) {   // 2 buffers x 4 classes x 5 float4 per path: any class may hold every path in flight
         RTW_CUDA(c, dalloc(pool, &w.sq, (size_t)2 * 4 * 5 * P));
@@ -33,8 +41,8 @@ static int ensure_wave(rtw_ctx* c, int P) {
     }
     RTW_CUDA(c, dalloc(pool, &w.counters, RTW_C_WORDS));
     w.P = P;
-    c->wave_capacity = P;
-    c->wave_stream = stream;
+    wv.capacity = P;
+    wv.for_stream = stream;
     return RTW_OK;
 }
 
@@ -53,23 +61,6 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     const unsigned long long npix = (unsigned long long)Nx * (unsigned long long)Ny;
     if (npix > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image too large");
     const unsigned long long total = npix * (unsigned long long)sample_count;
-    // Pool size (measured on the B200, tools/diag_tail.py, C2 at 32-1024 spp): 2^22 slots is the fastest at every
-    // frame length from 64 spp (23 M paths) up — 18.9 ms against 19.8 ms with 2^21 at 128 spp, the share one GPU
-    // of eight renders — while 2^24 slots lose 28 % (the gathers through the queues then span 2.7 GB).
-    // Option pool_paths overrides.
-    long long P = c->opt_pool_paths > 0 ? c->opt_pool_paths : (total >= (1ull << 23) ? (1ll << 22) : (1ll << 21));
-    if ((unsigned long long)P > total) P = (long long)std::max<unsigned long long>(total, 1024ull);
-    P = (P + 255) / 256 * 256;
-    int rc = ensure_wave(c, (int)P);
-    if (rc != RTW_OK) return rc;
-    DWave& w = c->wave;
-    w.accum = reinterpret_cast<float4*>(accum_dev);
-    w.Nx = Nx;
-    w.Ny = Ny;
-    w.max_depth = max_depth;
-    w.sample_first = sample_first;
-    w.sample_stride = sample_stride;
-    w.total = total;
 
     uint64_t launches = 0;
     rtw_stats& st = c->stats;
@@ -78,7 +69,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     st.build_ms = build_ms;
     RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
     if (max_depth == 0 && total > 0) {   // no ray is ever traced: black samples, counted
-        RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, w.accum, &launches));
+        RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, reinterpret_cast<float4*>(accum_dev), &launches));
         RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
         RTW_CUDA(c, cudaStreamSynchronize(c->stream));
         float ms0 = 0.f;
@@ -88,19 +79,59 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
         st.kernel_launches = launches;
         return RTW_OK;
     }
+
+    // Waves: the frame's samples are dealt round-robin to n_waves independent pools, each on its own stream.
+    // Their launches overlap on the device — while one wave's traversal launch saturates instruction issue,
+    // another's shading launch streams path state through HBM, and the tail of every launch (CTAs running out)
+    // is filled by the other wave's CTAs.  Measured on the B200, C2: 2666 -> 3042 Mpaths/s with two waves of 2^21
+    // slots against one of 2^22 (tools/dual_ctx.py).  A sample is the same random walk in whichever wave it runs
+    // (seed = tea<64>(pixel, k)), and every wave adds into the same accumulator with atomics.
+    int n_waves = c->opt_waves > 0 ? c->opt_waves : (total >= (1ull << 23) ? 2 : 1);
+    if (sample_count < n_waves) n_waves = sample_count > 0 ? sample_count : 1;
+    // Pool size (measured on the B200, tools/diag_tail.py, C2 at 32-1024 spp): 2^22 slots in total is the fastest
+    // at every frame length from 64 spp (23 M paths) up; 2^24 slots lose 28 % (the gathers through the queues then
+    // span 2.7 GB).  Option pool_paths overrides (slots per wave).
+    const long long P_all = total >= (1ull << 23) ? (1ll << 22) : (1ll << 21);
+    struct Run {
+        unsigned long long total = 0;
+        uint64_t iter = 0;
+        bool done = false, sparse = false, filled_prev = false;
+    } run[rtw_ctx::kMaxWaves];
     const bool stream = c->cfg.stream;
-    if (stream) RTW_CUDA(c, stream_init(c->stream, w, &launches));
-    else RTW_CUDA(c, wavefront_init(c->stream, w, &launches));
+    for (int j = 0; j < n_waves; j++) {
+        // wave j renders samples j, j + n_waves, ... of this call's samples
+        const int count_j = (sample_count - j + n_waves - 1) / n_waves;
+        run[j].total = npix * (unsigned long long)count_j;
+        long long P = c->opt_pool_paths > 0 ? c->opt_pool_paths : P_all / n_waves;
+        if ((unsigned long long)P > run[j].total) P = (long long)std::max<unsigned long long>(run[j].total, 1024ull);
+        P = (P + 255) / 256 * 256;
+        int rc = ensure_wave(c, j, (int)P);
+        if (rc != RTW_OK) return rc;
+        DWave& w = c->waves[j].w;
+        w.accum = reinterpret_cast<float4*>(accum_dev);
+        w.Nx = Nx;
+        w.Ny = Ny;
+        w.max_depth = max_depth;
+        w.sample_first = sample_first + j * sample_stride;
+        w.sample_stride = sample_stride * n_waves;
+        w.total = run[j].total;
+        w.trace_fill = 0;
+        w.trace_use = 0;
+        run[j].done = (run[j].total == 0);
+        cudaStream_t sj = c->waves[j].stream;
+        if (j > 0) RTW_CUDA(c, cudaStreamWaitEvent(sj, c->ev_begin, 0));   // the caller's work on `stream` (e.g. the clear) comes first
+        if (stream) RTW_CUDA(c, stream_init(sj, w, &launches));
+        else RTW_CUDA(c, wavefront_init(sj, w, &launches));
+    }
     const int lag = c->opt_lag;
-    uint64_t iter = 0;
-    bool done = (total == 0);
-    // Per-stage timing (option "profile"): CUDA events around the stages of SAMPLED
-    // iterations, read back after the frame — no host sync inside the frame.
+    // Per-stage timing (option "profile"): CUDA events around the stages of SAMPLED iterations of wave 0, read
+    // back after the frame — no host sync inside the frame.  With several waves the stages of wave 0 share the
+    // device with the other waves' launches, so their sum exceeds wave 0's share of the frame.
     const int kMaxSampled = 256;
     uint64_t prof_stride = 1;
     int sampled = 0;
     if (c->opt_profile) {
-        const uint64_t est = total / (uint64_t)P * 5 + 24;   // ~5 bounces per path
+        const uint64_t est = run[0].total / (uint64_t)c->waves[0].w.P * 5 + 24;   // ~5 bounces per path
         prof_stride = est / kMaxSampled + 1;
         while ((int)c->prof_events.size() < 5 * kMaxSampled) {
             cudaEvent_t e = nullptr;
@@ -111,43 +142,63 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     // Sparse mode: once the counters show fewer than half of the slots with a ray in flight (the drain tail of
     // the frame, or a frame smaller than the pool), the small-scene traversal walks a list of those slots —
     // kept by the shading and regeneration kernels from one iteration earlier — instead of scanning the pool.
-    bool sparse = false, filled_prev = false;
-    w.trace_fill = 0;
-    w.trace_use = 0;
-    while (!done) {
-        w.parity = (int)(iter & 1);
-        w.trace_fill = (sparse && c->cfg.small && !stream) ? 1 : 0;
-        w.trace_use = (w.trace_fill && filled_prev) ? 1 : 0;
-        filled_prev = w.trace_fill != 0;
-        cudaEvent_t* sev = nullptr;
-        if (c->opt_profile && sampled < kMaxSampled && iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
-        if (stream) RTW_CUDA(c, stream_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
-        else RTW_CUDA(c, wavefront_iteration(c->stream, c->scene, w, c->cfg, &launches, sev));
-        uint32_t* snap = c->h_counters + (iter % 8) * RTW_C_WORDS;
-        RTW_CUDA(c, cudaMemcpyAsync(snap, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, c->stream));
-        RTW_CUDA(c, cudaEventRecord(c->ring_events[iter % 8], c->stream));
-        iter++;
-        if (iter >= (uint64_t)lag) {
-            const uint64_t j = iter - lag;
-            RTW_CUDA(c, cudaEventSynchronize(c->ring_events[j % 8]));
-            const uint32_t* s = c->h_counters + (j % 8) * RTW_C_WORDS;
-            if (s[RTW_C_ALIVE] == 0) done = true;
-            if (s[RTW_C_ALIVE] < (uint32_t)(P / 2)) sparse = true;
+    bool all_done = false;
+    uint64_t iterations = 0;
+    while (!all_done) {
+        for (int j = 0; j < n_waves; j++) {
+            Run& r = run[j];
+            if (r.done) continue;
+            rtw_ctx::Wave& wv = c->waves[j];
+            DWave& w = wv.w;
+            w.parity = (int)(r.iter & 1);
+            w.trace_fill = (r.sparse && c->cfg.small && !stream) ? 1 : 0;
+            w.trace_use = (w.trace_fill && r.filled_prev) ? 1 : 0;
+            r.filled_prev = w.trace_fill != 0;
+            cudaEvent_t* sev = nullptr;
+            if (j == 0 && c->opt_profile && sampled < kMaxSampled && r.iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
+            if (stream) RTW_CUDA(c, stream_iteration(wv.stream, c->scene, w, c->cfg, &launches, sev));
+            else RTW_CUDA(c, wavefront_iteration(wv.stream, c->scene, w, c->cfg, &launches, sev));
+            uint32_t* snap = wv.h_counters + (r.iter % 8) * RTW_C_WORDS;
+            RTW_CUDA(c, cudaMemcpyAsync(snap, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, wv.stream));
+            RTW_CUDA(c, cudaEventRecord(wv.ring_events[r.iter % 8], wv.stream));
+            r.iter++;
+            if (r.iter > (1ull << 40)) return fail(c, RTW_ERR_STATE, "wavefront did not terminate");
         }
-        if (iter > (1ull << 40)) return fail(c, RTW_ERR_STATE, "wavefront did not terminate");
+        all_done = true;
+        for (int j = 0; j < n_waves; j++) {
+            Run& r = run[j];
+            if (r.done) continue;
+            if (r.iter >= (uint64_t)lag) {
+                rtw_ctx::Wave& wv = c->waves[j];
+                const uint64_t k = r.iter - lag;
+                RTW_CUDA(c, cudaEventSynchronize(wv.ring_events[k % 8]));
+                const uint32_t* s = wv.h_counters + (k % 8) * RTW_C_WORDS;
+                if (s[RTW_C_ALIVE] == 0) r.done = true;
+                if (s[RTW_C_ALIVE] < (uint32_t)(wv.w.P / 2)) r.sparse = true;
+            }
+            if (!r.done) all_done = false;
+        }
+    }
+    for (int j = 1; j < n_waves; j++) {   // the frame ends on `stream` when every wave has ended
+        RTW_CUDA(c, cudaEventRecord(c->waves[j].ev_done, c->waves[j].stream));
+        RTW_CUDA(c, cudaStreamWaitEvent(c->stream, c->waves[j].ev_done, 0));
     }
     RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
-    uint32_t* fin = c->h_counters;
-    RTW_CUDA(c, cudaMemcpyAsync(fin, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, c->stream));
-    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int j = 0; j < n_waves; j++)
+        RTW_CUDA(c, cudaMemcpyAsync(c->waves[j].h_counters, c->waves[j].w.counters, sizeof(uint32_t) * RTW_C_WORDS,
+                                    cudaMemcpyDeviceToHost, c->waves[j].stream));
+    for (int j = 0; j < n_waves; j++) RTW_CUDA(c, cudaStreamSynchronize(c->waves[j].stream));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, c->ev_begin, c->ev_end);
     st.render_ms = ms;
     st.paths = total;
-    st.rays_closest = u64_at(fin, RTW_C_RAYS_LO);
-    st.rays_shadow = u64_at(fin, RTW_C_SHRAYS_LO);
+    for (int j = 0; j < n_waves; j++) {
+        st.rays_closest += u64_at(c->waves[j].h_counters, RTW_C_RAYS_LO);
+        st.rays_shadow += u64_at(c->waves[j].h_counters, RTW_C_SHRAYS_LO);
+        iterations = std::max<uint64_t>(iterations, run[j].iter);
+    }
     st.kernel_launches = launches;
-    st.iterations = iter;
+    st.iterations = iterations;
     if (sampled > 0) {
         double a = 0, b = 0, d = 0, e = 0;
         for (int i = 0; i < sampled; i++) {
@@ -158,7 +209,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             cudaEventElapsedTime(&x, ev[2], ev[3]); d += x;
             cudaEventElapsedTime(&x, ev[3], ev[4]); e += x;
         }
-        const double scale = (double)iter / (double)sampled;   // extrapolate to all iterations
+        const double scale = (double)run[0].iter / (double)sampled;   // extrapolate to all iterations of wave 0
         st.logic_ms = a * scale; st.traverse_ms = b * scale; st.shade_ms = d * scale; st.shadow_ms = e * scale;
     }
     return RTW_OK;

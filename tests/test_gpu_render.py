@@ -125,6 +125,29 @@ def test_pool_size_and_lag_do_not_change_the_image(director, orc):
         assert np.allclose(imgs[0], im, rtol=1e-5, atol=1e-6)   # fp32 atomic order only
 
 
+@pytest.mark.parametrize("sid,Nx,Ny,spp", [(0, 64, 64, 9), (1, 64, 36, 6), (4, 48, 48, 5)])
+def test_waves_do_not_change_the_image(director, orc, sid, Nx, Ny, spp):
+    """A frame dealt to 1-4 concurrent pools (one stream each, samples round-robin) is the same image up to the
+    order of the fp32 atomic adds, with the same number of rays; small pools so that every wave turns over."""
+    director.init(Nx, Ny, spp)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    ref, c = o.render(Nx, Ny, spp, mode=1)
+    try:
+        director.set_option("pool_paths", 2048)
+        for waves in (1, 2, 3, 4):
+            director.set_option("waves", waves)
+            director.renderFrame(spp)
+            lin = director.linear()
+            st = director.stats()
+            assert np.all(lin[..., 3] == spp), waves
+            assert np.allclose(lin[..., :3], ref[..., :3] / spp, rtol=1e-5, atol=1e-6), waves
+            assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"], waves
+    finally:
+        director.set_option("waves", 0)
+        director.set_option("pool_paths", 0)
+
+
 def test_sample_sharding_matches_single_render(director, rtw):
     """Rank g of G renders samples k = g (mod G): two 'ranks' on one GPU."""
     torch = pytest.importorskip("torch")
