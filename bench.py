@@ -215,7 +215,8 @@ def main():
     out = torch.empty(NY, NX, 4, device=dev)
     host_img = torch.empty(NY, NX, 4).pin_memory()
     launches = {"n": 0}
-    agg = {"trav_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "logic_ms": 0.0, "render_ms": 0.0, "rays": 0, "shrays": 0, "iters": 0}
+    agg = {"trav_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "logic_ms": 0.0, "render_ms": 0.0, "rays": 0, "shrays": 0, "iters": 0,
+           "waves": 1, "pool": 0}
 
     def sync_all():
         if world > 1:
@@ -238,6 +239,7 @@ def main():
             agg["trav_ms"] += st["traverse_ms"]; agg["shadow_ms"] += st["shadow_ms"]; agg["shade_ms"] += st["shade_ms"]
             agg["logic_ms"] += st["logic_ms"]; agg["render_ms"] += st["render_ms"]
             agg["rays"] += st["rays_closest"]; agg["shrays"] += st["rays_shadow"]; agg["iters"] += st["iterations"]
+            agg["waves"] = st["waves"]; agg["pool"] = st["pool_paths"]
 
     def frame_e2e():
         """Same frame through the public API from HOST buffers: scene upload + LBVH build +
@@ -289,15 +291,15 @@ def main():
         value = paths / (dev_ms * 1e-3) / 1e6
         e2e = paths / (e2e_ms * 1e-3) / 1e6
         peak, peak_src = measured_peaks()
-        # pool size: the library's rule (api/rtw_render.cu) unless --pool overrides
-        pool = args.pool or ((1 << 22) if NX * NY * ((spp + world - 1) // world) >= (1 << 28) else (1 << 21))
+        pool, waves = int(agg["pool"]), int(agg["waves"])   # what the library chose (api/rtw_render.cu) or --pool / --opt waves=
         line = {"metric": METRIC, "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD if spp == SPP else WORKLOAD.replace("1024 spp", "%d spp (override)" % spp),
-                           "parallelism": "sample-sharded x%d, one NCCL reduce per frame" % world,
-                           "l2_policy": "inputs larger than L2: the wavefront pool (%d path slots per GPU x 160 B state + queues = %d MB) "
-                                        "streams through HBM every iteration, no flush between steps" % (pool, pool * 160 >> 20),
+                           "parallelism": "sample-sharded x%d, one NCCL reduce per frame; on each GPU the samples are dealt to "
+                                          "%d concurrent pools (waves) on separate streams" % (world, waves),
+                           "l2_policy": "inputs larger than L2: the wavefront pools (%d x %d path slots per GPU x 160 B state + queues = %d MB) "
+                                        "stream through HBM every iteration, no flush between steps" % (waves, pool, waves * pool * 160 >> 20),
                            "wall_ms_per_step": wall / args.steps * 1e3},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},
@@ -332,24 +334,47 @@ def main():
                                      ("k_regen", agg["logic_ms"], n_paths, 116.0)):
             gbs = units * bpu / max(ms * 1e-3, 1e-9) / 1e9
             stages[name] = {"ms_per_iteration": ms / iters, "units_per_iteration": units / iters, "bytes_per_unit": bpu,
-                            "gbs": gbs, "frac": gbs / peak, "share_of_render": ms / max(agg["render_ms"], 1e-9)}
+                            "gbs": gbs, "frac": gbs / peak, "kernel_ms_over_render_ms": ms / max(agg["render_ms"], 1e-9)}
+        ksum = sum(v["ms_per_iteration"] for v in stages.values())
         for name in stages:
             stages[name]["traffic"] = traffic_tab.get(name)
-        # the dominant kernel is the stage with the largest share of the frame
+            stages[name]["share_of_kernel_time"] = stages[name]["ms_per_iteration"] / max(ksum, 1e-12)
+        # the dominant kernel is the stage with the largest share of the kernel time
         dom = max(stages, key=lambda k: stages[k]["ms_per_iteration"])
         ds = stages[dom]
+        # the whole step against the same roof: algorithmic HBM bytes of every stage / device time of the frames
+        step_bytes = sum(v["units_per_iteration"] * v["bytes_per_unit"] for v in stages.values()) * iters
+        step_gbs = step_bytes / max(agg["render_ms"] * 1e-3, 1e-9) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ds["gbs"], "peak": peak, "unit": "GB/s",
                             "frac": ds["frac"], "traffic": ds["traffic"], "peak_source": peak_src,
                             "bytes_per_unit": ds["bytes_per_unit"], "units_per_launch": ds["units_per_iteration"],
                             "avg_launch_ms": ds["ms_per_iteration"],
+                            "step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_frame": step_bytes / max(args.steps, 1),
+                                     "note": "all stages' algorithmic HBM bytes / device time of the timed frames"},
                             "traversal_on_chip_bytes_per_ray_survey_8d": onchip_per_ray + 96.0,
                             "traversal_on_chip_gbs": agg["rays"] * onchip_per_ray / max(trav_s, 1e-9) / 1e9,
                             "note": "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured "
-                                    "live with CUDA events; traffic = dram bytes of one launch from the committed ncu capture. "
-                                    "k_shade* gathers 64-byte slot records through queue indices (latency-bound, ncu); the "
-                                    "traversal kernels are instruction-issue bound: a 13-primitive scene is one leaf range "
-                                    "passed by value, so their HBM share is only the state stream",
+                                    "live with CUDA events on wave 0's stream inside the timed frames; with %d waves a launch shares the "
+                                    "device with the other waves' launches, so per-launch figures understate what the GPU moves: "
+                                    "`step` is the whole frame against the same roof, `alone` the same kernels timed with one wave. "
+                                    "traffic = dram bytes of one launch from the committed ncu capture. k_shade* gathers 64-byte slot "
+                                    "records through queue indices; the traversal kernels are instruction-issue bound: a "
+                                    "13-primitive scene is one leaf range passed by value, so their HBM share is only the state "
+                                    "stream" % waves,
                             "stages": stages}
+        if waves > 1:   # the same kernels timed without a concurrent wave (one untimed extra frame)
+            d.set_option("waves", 1)
+            d.render_accum(accum.data_ptr(), 0, 1, max(spp // world, 1), DEPTH)
+            s1 = d.stats()
+            d.set_option("waves", 0)
+            it1 = max(s1["iterations"], 1)
+            key = {"k_traverse": "traverse_ms", "k_shade*": "shade_ms", "k_shadow": "shadow_ms", "k_regen": "logic_ms"}[dom]
+            units1 = {"k_traverse": s1["rays_closest"], "k_shade*": s1["rays_closest"], "k_shadow": s1["rays_shadow"],
+                      "k_regen": s1["paths"]}[dom]
+            g1 = units1 * ds["bytes_per_unit"] / max(s1[key] * 1e-3, 1e-9) / 1e9
+            line["roofline"]["alone"] = {"waves": 1, "pool_paths": int(s1["pool_paths"]), "avg_launch_ms": s1[key] / it1,
+                                         "units_per_launch": units1 / it1, "achieved": g1, "frac": g1 / peak,
+                                         "frame_ms": s1["render_ms"]}
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = cpu_sample(rtw, 15.0)
             line["cpu_baseline"] = cb

@@ -199,13 +199,18 @@ typedef struct rtw_stats {
     uint64_t rays_closest;      /* closest-hit traversals                       */
     uint64_t rays_shadow;       /* any-hit (shadow) traversals                  */
     uint64_t kernel_launches;   /* kernels launched by the last render          */
-    uint64_t iterations;        /* wavefront iterations of the last render      */
+    uint64_t iterations;        /* wavefront iterations of the last render, summed over its waves */
     double   render_ms;         /* device time of the last render (CUDA events) */
     double   build_ms;          /* device time of the last rtw_build_accel      */
+    /* option "profile": CUDA events around the stages of sampled iterations of wave 0, scaled to all
+     * iterations of all waves — i.e. summed kernel time; with more than one wave the launches of different
+     * waves overlap on the device, so the four figures add up to more than render_ms */
     double   traverse_ms;       /* device time inside k_traverse_closest, if profiling was enabled, else 0 */
     double   shadow_ms;         /* device time inside k_traverse_shadow, ditto  */
     double   shade_ms;          /* device time inside the shading kernels, ditto */
     double   logic_ms;          /* device time inside k_logic, ditto            */
+    uint64_t waves;             /* concurrent pools the last render was dealt to */
+    uint64_t pool_paths;        /* path slots per pool                          */
 } rtw_stats;
 
 typedef struct rtw_bvh_info {
@@ -308,8 +313,8 @@ void rtw_scene_free(rtw_scene* s);
  *      functions, scene/ioScene.h:180-982; here a flattened scene is a file) ------
  * rtw_scene_save writes `desc` (+ an optional description text) as one little-endian
  * file: magic "RTWS", version, header, the PODs above array by array, FNV-1a
- * checksum.  rtw_scene_load reads it back into an rtw_scene (free it with
- * rtw_scene_free) after validating sizes, checksum and every index a kernel follows.
+ * checksum.  rtw_scene_load reads it back into an rtw_scene, to be freed with
+ * rtw_scene_free, after validating sizes, checksum and every index a kernel follows.
  * RTW_ERR_IO: cannot open / short file; RTW_ERR_INVALID: not a scene file, wrong
  * version, checksum mismatch, index out of range.  rtw_scene_io_error(): the reason. */
 int  rtw_scene_save(const rtw_scene_desc* desc, const char* description, const char* path);

@@ -195,10 +195,12 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     for (int j = 0; j < n_waves; j++) {
         st.rays_closest += u64_at(c->waves[j].h_counters, RTW_C_RAYS_LO);
         st.rays_shadow += u64_at(c->waves[j].h_counters, RTW_C_SHRAYS_LO);
-        iterations = std::max<uint64_t>(iterations, run[j].iter);
+        iterations += run[j].iter;
     }
     st.kernel_launches = launches;
     st.iterations = iterations;
+    st.waves = (uint64_t)n_waves;
+    st.pool_paths = (uint64_t)c->waves[0].w.P;
     if (sampled > 0) {
         double a = 0, b = 0, d = 0, e = 0;
         for (int i = 0; i < sampled; i++) {
@@ -209,7 +211,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             cudaEventElapsedTime(&x, ev[2], ev[3]); d += x;
             cudaEventElapsedTime(&x, ev[3], ev[4]); e += x;
         }
-        const double scale = (double)run[0].iter / (double)sampled;   // extrapolate to all iterations of wave 0
+        const double scale = (double)iterations / (double)sampled;   // extrapolate to all iterations of all waves
         st.logic_ms = a * scale; st.traverse_ms = b * scale; st.shade_ms = d * scale; st.shadow_ms = e * scale;
     }
     return RTW_OK;
