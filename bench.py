@@ -364,7 +364,8 @@ def main():
                             "stages": stages}
         if waves > 1:   # the same kernels timed without a concurrent wave (one untimed extra frame)
             d.set_option("waves", 1)
-            d.render_accum(accum.data_ptr(), 0, 1, max(spp // world, 1), DEPTH)
+            for _ in range(2):      # the first frame re-allocates the pool
+                d.render_accum(accum.data_ptr(), 0, 1, max(spp // world, 1), DEPTH)
             s1 = d.stats()
             d.set_option("waves", 0)
             it1 = max(s1["iterations"], 1)
