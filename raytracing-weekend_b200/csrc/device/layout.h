@@ -178,6 +178,7 @@ struct SmallScene {
 #define RTW_C_SQ0        20                // 2 * 4 words
 #define RTW_C_NEW        28
 #define RTW_C_TRACED     29
+#define RTW_C_TICKET     30                // CTAs of k_regen that have finished (the last one retires the iteration's counters)
 #define RTW_C_WORDS      32
 
 // Per-slot state is read and written through queue indices (a warp of the shading kernels holds

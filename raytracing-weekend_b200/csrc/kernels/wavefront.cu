@@ -3,7 +3,7 @@
 // One iteration of the pool (replaces one trip of the `rayColor` while-loop of
 // raygen/raygen.cu:36-84 for every live path at once):
 //   k_regen       flush the paths that finished last iteration (compact queue), start new camera paths
-//   k_advance     retire the sample ordinals just handed out, clear the per-iteration counters
+//                 (its last CTA retires the sample ordinals just handed out and clears the per-iteration counters)
 //   k_traverse    closest-hit LBVH traversal + per-material queue compaction
 //   k_shade_all   the five material queues in one launch, one BSDF per CTA chunk: BSDF, NEE sample, Russian roulette
 //   k_shadow      any-hit traversal of the NEE rays, adds unoccluded contributions
@@ -44,6 +44,23 @@ __device__ __forceinline__ void queue_push_at(const DWave& w, int queue, int cou
     if (pred) w.queue[(size_t)queue * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
 }
 
+// After k_regen's last CTA (before k_traverse): the sample ordinals handed out by k_regen are retired and the
+// per-iteration counters (queue lengths, shadow count, rays in flight) are cleared.  One thread.
+__device__ __forceinline__ void advance_iteration(const DWave& w) {
+    unsigned long long* next = reinterpret_cast<unsigned long long*>(w.counters + RTW_C_NEXT_LO);
+    const unsigned long long n = (unsigned long long)w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+    if (w.trace_fill) {   // paths k_regen just started (ordinals next .. total - 1 of the n it looked at)
+        const unsigned long long left = *next < w.total ? w.total - *next : 0ull;
+        w.counters[RTW_C_TRACE0 + w.parity] += (uint32_t)(n < left ? n : left);
+        w.counters[RTW_C_TRACE0 + (w.parity ^ 1)] = 0u;   // filled by this iteration's shading for the next one
+    }
+    *next += n;
+    for (int k = 0; k < 8; k++) w.counters[k] = 0u;
+    w.counters[RTW_C_WORK_CLOSEST] = 0u;   // work counters of the persistent traversal warps
+    w.counters[RTW_C_WORK_SHADOW] = 0u;
+    w.counters[RTW_C_TICKET] = 0u;
+}
+
 // Regeneration: the slots whose path finished in the previous iteration (a compact
 // queue, so every lane of a warp does the same work) are flushed into the accumulator
 // and restarted with the next sample ordinal (raygen.cu:129-135, :141-158).
@@ -52,14 +69,14 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
     const uint32_t n = w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
     const unsigned long long next = *reinterpret_cast<const unsigned long long*>(w.counters + RTW_C_NEXT_LO);
     const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
-    // sparse mode: the restarted slots follow the survivors that the shading kernel listed (k_advance adds the count)
+    // sparse mode: the restarted slots follow the survivors that the shading kernel listed (advance_iteration adds the count)
     const uint32_t trace_base = w.trace_fill ? w.counters[RTW_C_TRACE0 + w.parity] : 0u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const uint32_t slot = q[i];
         // the old path's state is requested first, the new path (tea<64>: ~1000 integer instructions,
         // no memory) is computed while those loads are in flight, then flush, then store
         const float4 ra = w.rad[slot];
-        // queue position i takes sample ordinal next + i: no atomic (k_advance moves `next` on by n
+        // queue position i takes sample ordinal next + i: no atomic (advance_iteration moves `next` on by n
         // after this kernel)
         const unsigned long long ordinal = next + (unsigned long long)i;
         if (ordinal < w.total) {
@@ -72,25 +89,16 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
             retire_slot(w, slot);
         }
     }
-}
-
-// Between k_regen and k_traverse: the sample ordinals handed out by k_regen are retired and the
-// per-iteration counters (queue lengths, shadow count, rays in flight) are cleared.
-__global__ void k_advance(const DWave w) {
+    // The CTA that finishes last retires the iteration (every other CTA has read the queue length and `next`
+    // before it took its ticket): no separate one-warp launch between regeneration and traversal.
+    __syncthreads();
     if (threadIdx.x == 0) {
-        unsigned long long* next = reinterpret_cast<unsigned long long*>(w.counters + RTW_C_NEXT_LO);
-        const unsigned long long n = (unsigned long long)w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
-        if (w.trace_fill) {   // paths k_regen just started (ordinals next .. total - 1 of the n it looked at)
-            const unsigned long long left = *next < w.total ? w.total - *next : 0ull;
-            w.counters[RTW_C_TRACE0 + w.parity] += (uint32_t)(n < left ? n : left);
-            w.counters[RTW_C_TRACE0 + (w.parity ^ 1)] = 0u;   // filled by this iteration's shading for the next one
+        __threadfence();
+        if (atomicAdd(w.counters + RTW_C_TICKET, 1u) == gridDim.x - 1u) {
+            __threadfence();
+            advance_iteration(w);
         }
-        *next += n;
     }
-    __syncwarp();
-    if (threadIdx.x < 8) w.counters[threadIdx.x] = 0u;
-    if (threadIdx.x == 8) w.counters[RTW_C_WORK_CLOSEST] = 0u;   // work counters of the persistent traversal warps
-    if (threadIdx.x == 9) w.counters[RTW_C_WORK_SHADOW] = 0u;
 }
 
 // ---------------------------------------------------------------------------
@@ -657,8 +665,6 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     uint64_t l = 0;
     if (ev) cudaEventRecord(ev[0], s);
     k_regen<<<cfg.grid_logic, kBlock, 0, s>>>(sc, w);
-    l++;
-    k_advance<<<1, 32, 0, s>>>(w);
     l++;
     if (ev) cudaEventRecord(ev[1], s);
     if (cfg.small) k_traverse_small<<<cfg.grid_traverse, kBlock, 0, s>>>(sc, w, *cfg.small);
