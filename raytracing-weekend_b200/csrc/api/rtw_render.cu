@@ -67,8 +67,8 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     const double build_ms = st.build_ms;
     st = rtw_stats{};
     st.build_ms = build_ms;
-    RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
-    if (max_depth == 0 && total > 0) {   // no ray is ever traced: black samples, counted
+    if (max_depth == 0 && total > 0) {
+        RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));   // no ray is ever traced: black samples, counted
         RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, reinterpret_cast<float4*>(accum_dev), &launches));
         RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
         RTW_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -105,8 +105,11 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
         long long P = c->opt_pool_paths > 0 ? c->opt_pool_paths : P_all / n_waves;
         if ((unsigned long long)P > run[j].total) P = (long long)std::max<unsigned long long>(run[j].total, 1024ull);
         P = (P + 255) / 256 * 256;
-        int rc = ensure_wave(c, j, (int)P);
+        int rc = ensure_wave(c, j, (int)P);   // (re)allocation, if any, happens before the frame's clock starts
         if (rc != RTW_OK) return rc;
+    }
+    RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
+    for (int j = 0; j < n_waves; j++) {
         DWave& w = c->waves[j].w;
         w.accum = reinterpret_cast<float4*>(accum_dev);
         w.Nx = Nx;
