@@ -215,6 +215,7 @@ def main():
     out = torch.empty(NY, NX, 4, device=dev)
     host_img = torch.empty(NY, NX, 4).pin_memory()
     launches = {"n": 0}
+    trace = {}      # host-side wall time of the phases of a frame on this rank (rank 0's goes into the line)
     agg = {"trav_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "logic_ms": 0.0, "render_ms": 0.0, "rays": 0, "shrays": 0, "iters": 0,
            "waves": 1, "pool": 0}
 
@@ -225,15 +226,25 @@ def main():
 
     def frame(count_stats):
         """One frame with the scene resident: zero, render my samples, reduce, tonemap on root."""
-        sharding.render_frame_sharded(lambda f, sd, n: d.render_accum(accum.data_ptr(), f, sd, n, DEPTH),
-                                      accum, spp, rank, world)
+        ts = [time.perf_counter()]
+
+        def render_shard(f, sd, n):
+            ts.append(time.perf_counter())          # after zero + synchronize
+            d.render_accum(accum.data_ptr(), f, sd, n, DEPTH)
+            ts.append(time.perf_counter())          # after this rank's samples
+        sharding.render_frame_sharded(render_shard, accum, spp, rank, world)
         st = d.stats()
         n_l = st["kernel_launches"] + 1
         if world > 1:
             torch.cuda.synchronize()
+        ts.append(time.perf_counter())              # after the reduce
         if rank == 0:
             d.tonemap(accum.data_ptr(), out.data_ptr(), spp)
             n_l += 1
+        ts.append(time.perf_counter())
+        if count_stats:
+            for k, name in enumerate(("zero_ms", "render_call_ms", "reduce_ms", "tonemap_ms")):
+                trace[name] = trace.get(name, 0.0) + (ts[k + 1] - ts[k]) * 1e3
         if count_stats:
             launches["n"] += n_l
             agg["trav_ms"] += st["traverse_ms"]; agg["shadow_ms"] += st["shadow_ms"]; agg["shade_ms"] += st["shade_ms"]
@@ -300,7 +311,8 @@ def main():
                                           "%d concurrent pools (waves) on separate streams" % (world, waves),
                            "l2_policy": "inputs larger than L2: the wavefront pools (%d x %d path slots per GPU x 160 B state + queues = %d MB) "
                                         "stream through HBM every iteration, no flush between steps" % (waves, pool, waves * pool * 160 >> 20),
-                           "wall_ms_per_step": wall / args.steps * 1e3},
+                           "wall_ms_per_step": wall / args.steps * 1e3,
+                           "frame_phases_ms_rank0": {k: v / args.steps for k, v in trace.items()}},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},
                 "gpu_launches": int(tot[2].item()), "clocks": clk.summary()}

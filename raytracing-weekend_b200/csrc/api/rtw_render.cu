@@ -130,7 +130,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     // Per-stage timing (option "profile"): CUDA events around the stages of SAMPLED iterations of wave 0, read
     // back after the frame — no host sync inside the frame.  With several waves the stages of wave 0 share the
     // device with the other waves' launches, so their sum exceeds wave 0's share of the frame.
-    const int kMaxSampled = 256;
+    const int kMaxSampled = 64;    // (reading 5 events per sampled iteration back costs ~1.5 us each after the frame)
     uint64_t prof_stride = 1;
     int sampled = 0;
     if (c->opt_profile) {
