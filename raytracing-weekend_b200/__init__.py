@@ -270,7 +270,8 @@ class Director:
     def renderFrame(self, spp=None, max_depth=None):
         spp = self.Ns if spp is None else spp
         out = np.empty((self.Ny, self.Nx, 4), dtype=np.float32)
-        self._check(lib().rtw_render(self._c, self.Nx, self.Ny, spp, max_depth or self.max_depth, _ptr(out)),
+        depth = self.max_depth if max_depth is None else max_depth
+        self._check(lib().rtw_render(self._c, self.Nx, self.Ny, spp, depth, _ptr(out)),
                     "rtw_render")
         self.frame = out
         return out
@@ -281,8 +282,9 @@ class Director:
         return out
 
     def render_accum(self, accum_dev_ptr, sample_first, sample_stride, sample_count, max_depth=None):
+        depth = self.max_depth if max_depth is None else max_depth
         self._check(lib().rtw_render_accum(self._c, self.Nx, self.Ny, sample_first, sample_stride, sample_count,
-                                           max_depth or self.max_depth, C.c_void_p(accum_dev_ptr)), "rtw_render_accum")
+                                           depth, C.c_void_p(accum_dev_ptr)), "rtw_render_accum")
 
     def tonemap(self, accum_dev_ptr, out_dev_ptr, spp_total):
         self._check(lib().rtw_tonemap(self._c, self.Nx, self.Ny, spp_total, C.c_void_p(accum_dev_ptr),

@@ -1,0 +1,145 @@
+"""Edge cases of the hot path through the C-ABI, each against the oracle on the same inputs: ragged and
+one-pixel images, depth limits 0-3, empty and ragged ray sets, degenerate rays (zero direction, NaN, inverted
+interval, huge magnitudes), a one-primitive scene, sample counts that do not divide by the number of waves."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from rtw_types import RAY_DTYPE
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("sid,Nx,Ny", [(0, 1, 1), (0, 37, 3), (3, 5, 61), (1, 33, 7), (4, 17, 9)])
+def test_ragged_image_sizes_bit_exact(director, orc, sid, Nx, Ny):
+    director.init(Nx, Ny, 1)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    ref, c = o.render(Nx, Ny, 1, mode=1)
+    director.renderFrame(1)
+    assert np.array_equal(ref.view(np.uint32), director.linear().view(np.uint32))
+    st = director.stats()
+    assert st["paths"] == Nx * Ny and st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+
+
+@pytest.mark.parametrize("sid", [0, 1, 4])
+@pytest.mark.parametrize("depth", [0, 1, 2, 3])
+def test_depth_limits_bit_exact(director, orc, sid, depth):
+    """`while (depth < maxRayDepth)` (raygen/raygen.cu:36): limit 0 traces nothing (black, counted), 1 stops after
+    the first hit, ..."""
+    Nx, Ny = 40, 24
+    director.init(Nx, Ny, 1)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    ref, c = o.render(Nx, Ny, 1, max_depth=depth, mode=1)
+    out = director.renderFrame(1, max_depth=depth)
+    lin = director.linear()
+    assert np.array_equal(ref.view(np.uint32), lin.view(np.uint32))
+    st = director.stats()
+    assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+    if depth == 0:
+        assert not lin[..., :3].any() and np.all(lin[..., 3] == 1) and st["rays_closest"] == 0 and np.all(out[..., 3] == 1)
+
+
+@pytest.mark.parametrize("sid", [0, 4])
+def test_ragged_and_empty_ray_sets(director, orc, sid):
+    director.init(64, 64, 1)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    cam = director.camera_rays(0)
+    for n in (0, 1, 31, 32, 33, 255, 256, 257, 1000):
+        rays = cam[:n]
+        hits = director.trace_closest(rays)
+        occ = director.trace_any(rays)
+        assert len(hits) == n and len(occ) == n
+        if n:
+            rh, _ = o.trace_closest(rays, 0)
+            ro, _ = o.trace_any(rays, 0)
+            hits["t"][hits["prim"] < 0] = 0
+            rh["t"][rh["prim"] < 0] = 0
+            assert np.array_equal(hits, rh) and np.array_equal(occ, ro)
+
+
+@pytest.mark.parametrize("sid", [0, 1, 3, 4])
+def test_degenerate_rays_agree_with_the_oracle(director, orc, sid):
+    """Zero and denormal directions, NaN / inf components, an inverted or empty [tmin, tmax], axis-parallel rays in
+    the plane of a rect, huge origins: whatever the reference's arithmetic says, both sides must say the same."""
+    director.init(32, 32, 1)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    cam = director.camera_rays(0)
+    rays = np.zeros(0, dtype=RAY_DTYPE)
+    base = cam[[5, 300, 700, 1000]]
+
+    def variant(**kw):
+        r = base.copy()
+        for k, v in kw.items():
+            r[k] = v
+        return r
+    parts = [variant(dir=(0.0, 0.0, 0.0)), variant(dir=(0.0, 1.0, 0.0)), variant(dir=(1.0, 0.0, 0.0)), variant(dir=(0.0, 0.0, -1.0)),
+             variant(dir=(1e-42, 1.0, 0.0)), variant(dir=(np.nan, 1.0, 0.0)), variant(dir=(np.inf, 1.0, 0.0)),
+             variant(origin=(np.nan, 0.0, 0.0)), variant(origin=(1e30, 1e30, 1e30)), variant(origin=(278.0, 554.0, 279.5)),
+             variant(origin=(278.0, 0.0, 279.5), dir=(1.0, 0.0, 0.0)),       # in the plane of the floor
+             variant(tmin=10.0, tmax=1.0), variant(tmin=0.0, tmax=0.0), variant(tmin=-5.0, tmax=np.inf),
+             variant(dir=(1e20, 1e20, 1e20)), variant(dir=(-3e-39, -3e-39, 1.0))]
+    rays = np.concatenate(parts)
+    hits = director.trace_closest(rays)
+    occ = director.trace_any(rays)
+    rh, _ = o.trace_closest(rays, 0)
+    ro, _ = o.trace_any(rays, 0)
+    assert np.array_equal(hits["prim"], rh["prim"])
+    m = rh["prim"] >= 0
+    assert np.array_equal(hits["t"][m].view(np.uint32), rh["t"][m].view(np.uint32))
+    assert np.array_equal(occ, ro)
+
+
+def test_one_primitive_scene(director, rtw, orc):
+    """One leaf: the LBVH has no internal node worth the name; hits, misses and a 1 spp frame still agree."""
+    s = rtw.Scene(0, 32, 32)
+    d1 = rtw.SceneDesc.from_buffer_copy(s.desc.contents)
+    d1.n_prims = 1
+    p1 = C.pointer(d1)
+    director.init(32, 32, 1)
+    director.scene = s
+    director.upload(p1)
+    o = orc.OracleScene(p1, 1)
+    cam = director.camera_rays(0)
+    hits = director.trace_closest(cam)
+    rh, _ = o.trace_closest(cam, 0)
+    hits["t"][hits["prim"] < 0] = 0
+    rh["t"][rh["prim"] < 0] = 0
+    assert np.array_equal(hits, rh) and (rh["prim"] == 0).any() and (rh["prim"] == -1).any()
+    ref, c = o.render(32, 32, 1, mode=0)
+    director.renderFrame(1)
+    assert np.array_equal(ref.view(np.uint32), director.linear().view(np.uint32))
+    assert director.stats()["rays_closest"] == c["rays_closest"]
+
+
+def test_sample_counts_that_do_not_divide_by_the_waves(director, orc):
+    torch = pytest.importorskip("torch")
+    Nx = Ny = 32
+    director.init(Nx, Ny, 7)
+    director.createScene(0)
+    o = orc.OracleScene(director.scene.desc, 13)
+    acc = torch.zeros(Ny, Nx, 4, device="cuda:0")
+    torch.cuda.synchronize()
+    try:
+        director.set_option("waves", 4)
+        director.set_option("pool_paths", 1024)
+        director.render_accum(acc.data_ptr(), 0, 1, 0)               # nothing to do: returns, adds nothing
+        assert not acc.any().item()
+        director.render_accum(acc.data_ptr(), 3, 2, 1)               # one sample (k = 3): fewer samples than waves
+        ref, _ = o.render(Nx, Ny, 1, sample_first=3, sample_stride=2, mode=0)
+        assert np.array_equal(acc.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+        acc.zero_()
+        torch.cuda.synchronize()
+        director.render_accum(acc.data_ptr(), 1, 3, 7)               # k = 1, 4, ..., 19 dealt to 4 waves
+        ref, c = o.render(Nx, Ny, 7, sample_first=1, sample_stride=3, mode=0)
+        a = acc.cpu().numpy()
+        assert np.all(a[..., 3] == 7) and np.allclose(a, ref, rtol=1e-5, atol=1e-6)
+        st = director.stats()
+        assert st["waves"] == 4 and st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+    finally:
+        director.set_option("waves", 0)
+        director.set_option("pool_paths", 0)
