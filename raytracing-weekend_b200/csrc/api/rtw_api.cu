@@ -85,6 +85,7 @@ extern "C" int rtw_destroy(rtw_ctx* c) {
         if (wv.h_counters) cudaFreeHost(wv.h_counters);
         for (auto& e : wv.ring_events) if (e) cudaEventDestroy(e);
         if (wv.ev_done) cudaEventDestroy(wv.ev_done);
+        for (auto& e : wv.ev_iter) if (e) cudaEventDestroy(e);
         if (wv.stream && wv.stream != c->stream) cudaStreamDestroy(wv.stream);
     }
     free_frame(c);
@@ -133,6 +134,10 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "waves")) {
         if (value < 0 || value > rtw_ctx::kMaxWaves) return fail(c, RTW_ERR_INVALID, "waves out of range [0, 4] (0 = auto)");
         c->opt_waves = (int)value;
+    } else if (!strcmp(name, "lockstep")) {
+        c->opt_lockstep = value ? 1 : 0;
+    } else if (!strcmp(name, "stagger")) {
+        c->opt_stagger = value ? 1 : 0;
     } else if (!strcmp(name, "profile")) {
         c->opt_profile = value ? 1 : 0;
     } else if (!strcmp(name, "lag")) {

@@ -41,6 +41,7 @@ struct rtw_ctx {
         uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
         cudaEvent_t ring_events[8] = {};
         cudaEvent_t ev_done = nullptr;
+        cudaEvent_t ev_iter[2] = {};        // lockstep: recorded at the start of even / odd iterations
     };
     Wave waves[kMaxWaves];
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
@@ -64,6 +65,8 @@ struct rtw_ctx {
     int opt_stream = -1;             // -1 = auto (rtw_build_accel), 0 = slot pool, 1 = streaming wavefront
     int opt_grid_pct = 100;          // share of the resident-CTA grids one context launches (two contexts on one GPU: 50)
     int opt_waves = 0;               // 0 = auto (rtw_render.cu), else 1..4 concurrent pools per frame
+    int opt_stagger = 0;             // odd waves start half an iteration after their even neighbour (measured slower)
+    int opt_lockstep = 0;            // iteration i of every wave starts when all waves have finished iteration i - 1 (measured slower)
     int opt_profile = 0;
     int opt_lag = 3;
 

@@ -16,6 +16,7 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
         else RTW_CUDA(c, cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
         for (auto& e : wv.ring_events) RTW_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         RTW_CUDA(c, cudaEventCreateWithFlags(&wv.ev_done, cudaEventDisableTiming));
+        for (auto& e : wv.ev_iter) RTW_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         RTW_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&wv.h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8));
     }
     if (wv.capacity >= P && wv.for_stream == stream) {
@@ -148,6 +149,22 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     bool all_done = false;
     uint64_t iterations = 0;
     while (!all_done) {
+        // Phase experiments (options, both OFF by default; tools/gpu_variants.sh, three runs each, C2): the waves
+        // left to run freely settle half-way between "same stage side by side" and "opposite stages" and render
+        // 3040-3053 Mpaths/s; forced into LOCKSTEP (iteration i of every wave starts when all waves have finished
+        // iteration i - 1) 2939-2942; started half an iteration apart (STAGGER) 2927-2976.
+        if (c->opt_lockstep && n_waves > 1) {
+            int live = 0;
+            for (int j = 0; j < n_waves; j++) live += run[j].done ? 0 : 1;
+            if (live > 1) {
+                for (int j = 0; j < n_waves; j++)
+                    if (!run[j].done) RTW_CUDA(c, cudaEventRecord(c->waves[j].ev_iter[run[j].iter & 1], c->waves[j].stream));
+                for (int j = 0; j < n_waves; j++)
+                    for (int k = 0; k < n_waves; k++)
+                        if (k != j && !run[j].done && !run[k].done)
+                            RTW_CUDA(c, cudaStreamWaitEvent(c->waves[j].stream, c->waves[k].ev_iter[run[k].iter & 1], 0));
+            }
+        }
         for (int j = 0; j < n_waves; j++) {
             Run& r = run[j];
             if (r.done) continue;
@@ -159,8 +176,14 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             r.filled_prev = w.trace_fill != 0;
             cudaEvent_t* sev = nullptr;
             if (j == 0 && c->opt_profile && sampled < kMaxSampled && r.iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
-            if (stream) RTW_CUDA(c, stream_iteration(wv.stream, c->scene, w, c->cfg, &launches, sev));
-            else RTW_CUDA(c, wavefront_iteration(wv.stream, c->scene, w, c->cfg, &launches, sev));
+            LaunchCfg cfg = c->cfg;
+            cfg.mid_event = nullptr;
+            if (c->opt_stagger && r.iter == 0 && n_waves > 1) {
+                if ((j & 1) == 0 && j + 1 < n_waves) cfg.mid_event = wv.ev_done;
+                if (j & 1) RTW_CUDA(c, cudaStreamWaitEvent(wv.stream, c->waves[j - 1].ev_done, 0));
+            }
+            if (stream) RTW_CUDA(c, stream_iteration(wv.stream, c->scene, w, cfg, &launches, sev));
+            else RTW_CUDA(c, wavefront_iteration(wv.stream, c->scene, w, cfg, &launches, sev));
             uint32_t* snap = wv.h_counters + (r.iter % 8) * RTW_C_WORDS;
             RTW_CUDA(c, cudaMemcpyAsync(snap, w.counters, sizeof(uint32_t) * RTW_C_WORDS, cudaMemcpyDeviceToHost, wv.stream));
             RTW_CUDA(c, cudaEventRecord(wv.ring_events[r.iter % 8], wv.stream));

@@ -59,6 +59,7 @@ struct LaunchCfg {
     bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
     bool stream;            // streaming wavefront (kernels/stream.cu) instead of the slot pool (kernels/wavefront.cu)
     int grid_fill, grid_stream;   // its two grids
+    cudaEvent_t mid_event;  // if set: recorded in the middle of the iteration (after the traversal / fill launch)
     const SmallScene* small; // host copy of a <= RTW_SMALL_MAX-leaf scene passed to the *_small kernels by value (else null)
 };
 cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg);

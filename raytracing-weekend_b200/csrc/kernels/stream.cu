@@ -262,6 +262,7 @@ cudaError_t stream_iteration(cudaStream_t s, const DScene& sc, const DWave& w, c
     if (ev) cudaEventRecord(ev[0], s);
     if (cfg.small) k_stream_fill_small<<<cfg.grid_fill, kBlock, 0, s>>>(sc, w, *cfg.small);
     else k_stream_fill_bvh<<<cfg.grid_fill, kBlock, cfg.smem_top, s>>>(sc, w);
+    if (cfg.mid_event) cudaEventRecord(cfg.mid_event, s);
     if (ev) { cudaEventRecord(ev[1], s); cudaEventRecord(ev[2], s); }
     if (cfg.small) {
         if (cfg.shade_ctas == 2) k_stream_shade_small<2><<<cfg.grid_stream, kBlock, 0, s>>>(sc, w, *cfg.small, classes, shadow);

@@ -671,6 +671,7 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     else if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
     else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
     l++;
+    if (cfg.mid_event) cudaEventRecord(cfg.mid_event, s);
     if (ev) cudaEventRecord(ev[2], s);
     const uint32_t classes = cfg.class_mask | (1u << RTW_Q_TERMINAL);
     if (cfg.shade_ctas == 2) k_shade_all<2><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
