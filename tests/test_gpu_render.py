@@ -200,6 +200,28 @@ def test_c2_full_size_properties(director, orc):
     assert np.array_equal(ref1.view(np.uint32), director.linear().view(np.uint32))
 
 
+@pytest.mark.parametrize("sid,Nx,Ny", [(1, 1920, 1080), (4, 800, 800)])
+def test_c3_c4_full_size_first_sample_bit_exact(director, orc, sid, Nx, Ny):
+    """The image sizes of BASELINE.json's C3 (Book-1 final, 1920x1080) and C4 (Book-2 final, 800x800): sample 0 of
+    every pixel is the same bits as the oracle's (its LBVH mirror, all host threads), with the same ray counts;
+    two more samples per pixel agree up to the order of the atomic adds and leave a finite, non-negative image."""
+    director.init(Nx, Ny, 3)
+    director.createScene(sid)
+    o = orc.OracleScene(director.scene.desc, director.scene.desc.contents.n_prims)
+    ref, c = o.render(Nx, Ny, 1, mode=1)
+    director.renderFrame(1)
+    assert np.array_equal(ref.view(np.uint32), director.linear().view(np.uint32))
+    st = director.stats()
+    assert st["paths"] == Nx * Ny and st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"]
+    ref3, c3 = o.render(Nx, Ny, 3, mode=1)
+    director.renderFrame(3)
+    lin = director.linear()
+    st = director.stats()
+    assert np.all(lin[..., 3] == 3) and np.isfinite(lin).all() and (lin[..., :3] >= 0).all()
+    assert np.allclose(lin[..., :3], ref3[..., :3] / 3, rtol=1e-5, atol=1e-6)
+    assert st["rays_closest"] == c3["rays_closest"] and st["rays_shadow"] == c3["rays_shadow"]
+
+
 def test_profile_option_reports_stage_times(director):
     director.init(64, 64, 2)
     director.createScene(0)
