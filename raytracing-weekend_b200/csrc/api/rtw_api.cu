@@ -134,6 +134,9 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "waves")) {
         if (value < 0 || value > rtw_ctx::kMaxWaves) return fail(c, RTW_ERR_INVALID, "waves out of range [0, 4] (0 = auto)");
         c->opt_waves = (int)value;
+    } else if (!strcmp(name, "tail_paths")) {
+        if (value < 0 || value > (1 << 22)) return fail(c, RTW_ERR_INVALID, "tail_paths out of range [0, 2^22]");
+        c->opt_tail_paths = (int)value;
     } else if (!strcmp(name, "lockstep")) {
         c->opt_lockstep = value ? 1 : 0;
     } else if (!strcmp(name, "stagger")) {

@@ -96,7 +96,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     struct Run {
         unsigned long long total = 0;
         uint64_t iter = 0;
-        bool done = false, sparse = false, filled_prev = false;
+        bool done = false, sparse = false, filled_prev = false, tail = false;
     } run[rtw_ctx::kMaxWaves];
     const bool stream = c->cfg.stream;
     for (int j = 0; j < n_waves; j++) {
@@ -171,6 +171,14 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             rtw_ctx::Wave& wv = c->waves[j];
             DWave& w = wv.w;
             w.parity = (int)(r.iter & 1);
+            if (r.tail) {
+                // Drain tail (kernels/stream.cu k_tail_*): no sample left to start and few paths alive — instead of
+                // ~30 more iterations of four nearly empty launches, one launch runs every surviving path to its end.
+                w.trace_use = r.filled_prev ? 1 : 0;   // the last shading launch listed the survivors (sparse mode)
+                RTW_CUDA(c, launch_tail(wv.stream, c->scene, w, c->cfg, &launches));
+                r.done = true;
+                continue;
+            }
             w.trace_fill = (r.sparse && c->cfg.small && !stream) ? 1 : 0;
             w.trace_use = (w.trace_fill && r.filled_prev) ? 1 : 0;
             r.filled_prev = w.trace_fill != 0;
@@ -201,6 +209,9 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
                 const uint32_t* s = wv.h_counters + (k % 8) * RTW_C_WORDS;
                 if (s[RTW_C_ALIVE] == 0) r.done = true;
                 if (s[RTW_C_ALIVE] < (uint32_t)(wv.w.P / 2)) r.sparse = true;
+                if (!stream && c->opt_tail_paths > 0 && s[RTW_C_ALIVE] < (uint32_t)c->opt_tail_paths &&
+                    u64_at(s, RTW_C_NEXT_LO) >= r.total)
+                    r.tail = true;
             }
             if (!r.done) all_done = false;
         }

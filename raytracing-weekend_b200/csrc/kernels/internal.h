@@ -72,6 +72,10 @@ cudaError_t stream_configure(const DScene& sc, LaunchCfg* cfg);
 cudaError_t stream_init(cudaStream_t s, const DWave& w, uint64_t* launches);
 cudaError_t stream_iteration(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg,
                              uint64_t* launches, cudaEvent_t* stage_events /* 5 or null */);
+// Drain tail of a slot-pool frame in one launch pair (kernels/stream.cu): flush the slots that finished in the
+// last iteration, then one thread per surviving path runs it to its end.  w.parity = parity of the iteration that
+// is NOT run; w.trace_use = the sparse-mode list of survivors is valid (else the pool is scanned).
+cudaError_t launch_tail(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg, uint64_t* launches);
 cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches);
 cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
 

@@ -210,6 +210,112 @@ __global__ void k_stream_init(const DWave w) {
     }
 }
 
+// ---------------------------------------------------------------------------
+// Drain tail of a SLOT-POOL frame (kernels/wavefront.cu) in one launch.
+//
+// When no sample is left to start, the population of a pool decays by ~30 % per iteration and the last
+// ~30 iterations each cost four launches for a few thousand rays: launch latency, not work (0.6-0.9 ms per
+// frame, 5 % of the 17 ms frame one GPU of eight renders).  Once fewer than `tail_paths` paths are alive the
+// host stops iterating and launches k_tail_flush (the slots that finished in the last iteration go to the
+// accumulator, as k_regen would do) and k_tail_*: one THREAD per surviving path runs it to its end — trace,
+// terminal vertex or BSDF + NEE + shadow ray + Russian roulette, next ray — with the per-thread bodies of the
+// streaming wavefront (device/stream.h), i.e. the same statements in the same order as the staged kernels.
+__device__ __forceinline__ PathV path_of_slot(const DWave& w, uint32_t slot) {
+    const RayRec ray = w.rec[slot].ray;
+    const PathRec st = w.rec[slot].st;
+    const float4 ra = w.rad[slot];
+    PathV p;
+    p.o = f3(ray.o); p.time = ray.o.w;
+    p.d = f3(ray.d); p.gather = ray.d.w;
+    p.thr = f3(st.thr); p.seed = f2u(st.thr.w);
+    p.depth = misc_depth(st.misc.x); p.lseed = st.misc.y;
+    p.t = 0.f; p.leaf = RTW_REF_NONE;
+    p.rad = f3(ra); p.pixel = f2u(ra.w);
+    return p;
+}
+
+__global__ void __launch_bounds__(kBlock) k_tail_flush(const DWave w) {
+    const uint32_t n = w.counters[RTW_C_QUEUE0 + RTW_Q_REGEN];
+    const uint32_t* q = w.queue + (size_t)RTW_Q_REGEN * w.P;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = q[i];
+        logic_flush(w, w.rad[slot]);
+        retire_slot(w, slot);      // k_tail_* may find its paths by scanning the pool: this slot holds none any more
+    }
+}
+
+template <class Trav>
+__device__ __forceinline__ void tail_run(const DScene& sc, const DWave& w, const Trav& trav, bool has_shadow) {
+    // the paths: the list the last shading launch kept (sparse mode), or every slot that holds a ray
+    const bool listed = w.trace_use != 0;
+    const uint32_t n = listed ? w.counters[RTW_C_TRACE0 + w.parity] : (uint32_t)w.P;
+    const uint32_t* list = w.queue + (size_t)RTW_Q_TRACE * w.P;
+    const uint32_t tiles = (n + kBlock - 1) / kBlock;
+    uint32_t n_closest = 0, n_shadow = 0;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t i = tile * kBlock + threadIdx.x;
+        bool alive = i < n;
+        PathV p{};
+        if (alive) {
+            const uint32_t slot = listed ? list[i] : i;
+            alive = f2u(w.rec[slot].ray.o.w) != RTW_RAY_NONE;
+            if (alive) p = path_of_slot(w, slot);
+        }
+        while (__any_sync(0xffffffffu, alive)) {
+            RayW r = idle_ray(1e-6f, 0.f);
+            if (alive) r = closest_ray(p);
+            float t;
+            uint32_t leaf;
+            const bool found = trav.closest(r, alive, t, leaf);
+            int cls = -1;
+            if (alive) {
+                n_closest++;
+                cls = classify_or_finish<MemGlobal>(sc, w, p, found, t, leaf);   // terminal vertex: shaded and flushed
+                if (cls < 0) alive = false;
+            }
+            ShadowOut sh;
+            sh.emit = false;
+            bool goes_on = false;
+            if (alive) goes_on = shade_core<MemGlobal>(sc, w.max_depth, cls, p, sh);
+            __syncwarp();
+            if (has_shadow && __any_sync(0xffffffffu, sh.emit)) {
+                RayW q = idle_ray(500 * 1.0e-7f, 0.f);
+                if (sh.emit) {
+                    q.o = sh.o; q.d = sh.d; q.tmax = sh.tmax;
+                    q.gather = sc.has_motion ? p.gather : 0.f;
+                    q.seed = sh.seed;
+                    n_shadow++;
+                }
+                const bool occluded = trav.any(q, sh.emit);
+                if (sh.emit && !occluded) {
+                    p.rad.x += sh.contrib.x; p.rad.y += sh.contrib.y; p.rad.z += sh.contrib.z;
+                }
+            }
+            if (alive && !goes_on) {
+                path_flush(w, p);
+                alive = false;
+            }
+        }
+    }
+    n_closest = __reduce_add_sync(0xffffffffu, n_closest);
+    n_shadow = __reduce_add_sync(0xffffffffu, n_shadow);
+    if ((threadIdx.x & 31u) == 0) {
+        if (n_closest) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + RTW_C_RAYS_LO), (unsigned long long)n_closest);
+        if (n_shadow) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + RTW_C_SHRAYS_LO), (unsigned long long)n_shadow);
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_tail_small(const DScene sc, const DWave w, const __grid_constant__ SmallScene ss, int has_shadow) {
+    tail_run(sc, w, TravStreamSmall{ss}, has_shadow != 0);
+}
+__global__ void __launch_bounds__(kBlock) k_tail_bvh(const DScene sc, const DWave w, int has_shadow) {
+    extern __shared__ float4 s_top[];
+    const int n4 = 4 * sc.n_top;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) s_top[i] = __ldg(sc.top_nodes + i);
+    __syncthreads();
+    tail_run(sc, w, TravStreamBvh{sc, s_top}, has_shadow != 0);
+}
+
 template <class K>
 int resident_grid(K kernel, size_t smem, int sms) {
     int per_sm = 0;
@@ -234,6 +340,8 @@ cudaError_t stream_configure(const DScene& sc, LaunchCfg* cfg) {
         if (cfg->smem_top > 48 * 1024) {
             e = cudaFuncSetAttribute(k_stream_fill_bvh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
             if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(k_tail_bvh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
+            if (e != cudaSuccess) return e;
             e = cudaFuncSetAttribute(k_stream_shade_bvh<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
             if (e != cudaSuccess) return e;
             e = cudaFuncSetAttribute(k_stream_shade_bvh<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg->smem_top);
@@ -247,6 +355,15 @@ cudaError_t stream_configure(const DScene& sc, LaunchCfg* cfg) {
                                                 : resident_grid(k_stream_shade_bvh<3>, cfg->smem_top, sms);
     }
     return cudaSuccess;
+}
+
+cudaError_t launch_tail(cudaStream_t s, const DScene& sc, const DWave& w, const LaunchCfg& cfg, uint64_t* launches) {
+    k_tail_flush<<<148, kBlock, 0, s>>>(w);
+    const int grid = cfg.grid_fill > 0 ? cfg.grid_fill : 148;
+    if (cfg.small) k_tail_small<<<grid, kBlock, 0, s>>>(sc, w, *cfg.small, cfg.has_shadow ? 1 : 0);
+    else k_tail_bvh<<<grid, kBlock, cfg.smem_top, s>>>(sc, w, cfg.has_shadow ? 1 : 0);
+    if (launches) *launches += 2;
+    return cudaGetLastError();
 }
 
 cudaError_t stream_init(cudaStream_t s, const DWave& w, uint64_t* launches) {

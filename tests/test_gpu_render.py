@@ -111,15 +111,17 @@ def test_pool_size_and_lag_do_not_change_the_image(director, orc):
         for stream in (1, 0):
             director.set_option("stream", stream)
             director.createScene(0)
-            for pool, lag in ((1024, 1), (4096, 3), (1 << 16, 7)):
+            for pool, lag, tail in ((1024, 1, 0), (4096, 3, 300), (1 << 16, 7, 32768), (2048, 2, 1 << 20)):
                 director.set_option("pool_paths", pool)
                 director.set_option("lag", lag)
+                director.set_option("tail_paths", tail)
                 director.renderFrame(8)
                 imgs.append(director.linear())
                 assert director.stats()["paths"] == Nx * Ny * 8 and np.all(imgs[-1][..., 3] == 8)
     finally:
         director.set_option("pool_paths", 0)
         director.set_option("lag", 3)
+        director.set_option("tail_paths", 131072)
         director.set_option("stream", -1)
     for im in imgs[1:]:
         assert np.allclose(imgs[0], im, rtol=1e-5, atol=1e-6)   # fp32 atomic order only
@@ -255,6 +257,8 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
     ref = None
     try:
         for opts in ({"stream": 0, "walker": 0, "small": 0}, {"stream": 0, "walker": 0, "small": 1},
+                     {"stream": 0, "walker": 0, "small": 0, "tail_paths": 0}, {"stream": 0, "walker": 0, "small": 1, "tail_paths": 0},
+                     {"stream": 0, "walker": 0, "small": 1, "tail_paths": 1 << 22},
                      {"stream": 1, "walker": 0, "small": 1}, {"stream": 1, "walker": 0, "small": 0},
                      {"stream": 1, "walker": 0, "small": 0, "shade_ctas": 2}, {"stream": 1, "walker": 0, "small": 1, "shade_ctas": 4},
                      {"stream": 0, "shade_ctas": 3, "walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
@@ -273,5 +277,6 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             rh, _ = o.trace_closest(director.camera_rays(0), 1)
             assert np.array_equal(hits, rh)
     finally:
-        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22}.items():
+        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22,
+                     "tail_paths": 131072}.items():
             director.set_option(k, v)
