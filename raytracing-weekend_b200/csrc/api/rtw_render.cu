@@ -171,6 +171,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
             rtw_ctx::Wave& wv = c->waves[j];
             DWave& w = wv.w;
             w.parity = (int)(r.iter & 1);
+            w.first_iter = r.iter == 0 ? 1 : 0;
             if (r.tail) {
                 // Drain tail (kernels/stream.cu k_tail_*): no sample left to start and few paths alive — instead of
                 // ~30 more iterations of four nearly empty launches, one launch runs every surviving path to its end.

@@ -222,6 +222,7 @@ struct DWave {
     int parity;                 // iteration index & 1
     int trace_fill;             // shading and regeneration list the slots the NEXT / this traversal must trace
     int trace_use;              // this iteration's traversal walks the list (filled since the previous iteration)
+    int first_iter;             // first iteration of a frame: every slot is free and holds nothing (k_regen takes slot i, reads nothing)
 };
 
 }  // namespace rtw

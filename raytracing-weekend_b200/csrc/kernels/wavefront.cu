@@ -72,10 +72,12 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
     // sparse mode: the restarted slots follow the survivors that the shading kernel listed (advance_iteration adds the count)
     const uint32_t trace_base = w.trace_fill ? w.counters[RTW_C_TRACE0 + w.parity] : 0u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint32_t slot = q[i];
+        // first iteration of a frame: the pool is empty, slot i is free and there is nothing to flush (no pass
+        // over the pool to say so: k_wave_init only sets the counters)
+        const uint32_t slot = w.first_iter ? i : q[i];
         // the old path's state is requested first, the new path (tea<64>: ~1000 integer instructions,
         // no memory) is computed while those loads are in flight, then flush, then store
-        const float4 ra = w.rad[slot];
+        const float4 ra = w.first_iter ? make_float4(0.f, 0.f, 0.f, u2f(RTW_PIXEL_NONE)) : w.rad[slot];
         // queue position i takes sample ordinal next + i: no atomic (advance_iteration moves `next` on by n
         // after this kernel)
         const unsigned long long ordinal = next + (unsigned long long)i;
@@ -493,11 +495,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave 
 
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) k_wave_init(const DWave w) {
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < (uint32_t)w.P; slot += stride) {
-        retire_slot(w, slot);
-        w.queue[(size_t)RTW_Q_REGEN * w.P + slot] = slot;   // every slot is free: the first k_regen fills the pool
-    }
+    // every slot is free: the first k_regen (DWave::first_iter) fills slots 0 .. P-1 and retires those past the last sample
     if (blockIdx.x == 0 && threadIdx.x < RTW_C_WORDS)
         w.counters[threadIdx.x] = (threadIdx.x == RTW_C_QUEUE0 + RTW_Q_REGEN) ? (uint32_t)w.P : 0u;
 }
@@ -655,7 +653,7 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
 }
 
 cudaError_t wavefront_init(cudaStream_t s, const DWave& w, uint64_t* launches) {
-    k_wave_init<<<296, kBlock, 0, s>>>(w);
+    k_wave_init<<<1, kBlock, 0, s>>>(w);
     if (launches) *launches += 1;
     return cudaGetLastError();
 }
