@@ -35,46 +35,83 @@ def host_cores():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """SM clocks + throttle reasons DURING the timed region (B200_PROFILING.md's clocks line).  Read through NVML
+    inside this process (the same counters nvidia-smi prints; initialised BEFORE the timed region) by rank 0 for every
+    GPU of the run: one `nvidia-smi` process per rank starting inside a 50 ms timed region cost the 8-GPU run 5 %.
+    Falls back to the nvidia-smi query of the recipe if NVML cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = (("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40))
 
-    def __init__(self, gpu_index):
-        self.rows = []
-        self.gpu = gpu_index
+    def __init__(self, gpu_indices, enabled=True):
+        self.rows = []          # (sm_mhz, sm_max_mhz, power_w, [reasons])
+        self.gpus = list(gpu_indices)
+        self.enabled = enabled
         self.stop = threading.Event()
         self.th = threading.Thread(target=self._run, daemon=True)
+        self.nvml = None
+        self.handles = []
+        self.source = "none"
+        if not enabled:
+            return
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.handles = [pynvml.nvmlDeviceGetHandleByIndex(i) for i in self.gpus]
+            self.nvml = pynvml
+            self.source = "nvml"
+        except Exception:
+            self.source = "nvidia-smi"
+
+    def _sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            for h in self.handles:
+                try:
+                    sm = float(n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM))
+                    mx = float(n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM))
+                    pw = n.nvmlDeviceGetPowerUsage(h) / 1000.0
+                    get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+                    mask = int(get(h))
+                    self.rows.append((sm, mx, pw, [name for name, bit in self.BITS if mask & bit]))
+                except Exception:
+                    pass
+            return
+        try:
+            out = subprocess.run(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-i",
+                                  ",".join(str(i) for i in self.gpus)], capture_output=True, text=True, timeout=5).stdout.strip()
+            for line in out.splitlines():
+                r = [c.strip() for c in line.split(",")]
+                reasons = [name for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9])
+                           if v.lower().startswith("active")]
+                self.rows.append((float(r[1]), float(r[2]), float(r[3]), reasons))
+        except Exception:
+            pass
 
     def _run(self):
         while not self.stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-i", str(self.gpu)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
-            except Exception:
-                pass
-            self.stop.wait(0.2)
+            self._sample()
+            self.stop.wait(0.02 if self.nvml is not None else 0.2)
 
     def __enter__(self):
-        self.th.start()
+        if self.enabled:
+            self.th.start()
         return self
 
     def __exit__(self, *a):
         self.stop.set()
-        self.th.join(timeout=6)
+        if self.enabled:
+            self.th.join(timeout=6)
 
     def summary(self):
         if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit())
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"], "source": self.source}
+        sm = sorted(r[0] for r in self.rows)
         reasons = set()
         for r in self.rows:
-            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][2]),
-                "power_w_max": max(float(r[3]) for r in self.rows), "samples": len(self.rows), "reasons": sorted(reasons)}
+            reasons.update(r[3])
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.rows[0][1], "power_w_max": max(r[2] for r in self.rows),
+                "samples": len(self.rows), "reasons": sorted(reasons), "source": self.source, "gpus": self.gpus}
 
 
 def measured_peaks():
@@ -265,7 +302,7 @@ def main():
         frame(False)
     sync_all()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
+    with ClockSampler(list(range(world)) if world > 1 else [local], enabled=(rank == 0)) as clk:
         ev0.record()
         t0 = time.perf_counter()
         for _ in range(args.steps):
