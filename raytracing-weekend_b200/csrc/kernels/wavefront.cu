@@ -30,20 +30,6 @@ __device__ __forceinline__ void stage_top(const DScene& sc, float4* s_top) {
     __syncthreads();
 }
 
-// ---------------------------------------------------------------------------
-// Warp-aggregated push of `slot` onto queue `cls` for the lanes where `pred` holds:
-// one ballot + one atomicAdd per warp.
-__device__ __forceinline__ void queue_push_at(const DWave& w, int queue, int counter, bool pred, uint32_t slot) {
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t mask = __ballot_sync(0xffffffffu, pred);
-    if (!mask) return;
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(w.counters + counter, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (pred) w.queue[(size_t)queue * w.P + base + __popc(mask & ((1u << lane) - 1u))] = slot;
-}
-
 // After k_regen's last CTA (before k_traverse): the sample ordinals handed out by k_regen are retired and the
 // per-iteration counters (queue lengths, shadow count, rays in flight) are cleared.  One thread.
 __device__ __forceinline__ void advance_iteration(const DWave& w) {

@@ -6,7 +6,7 @@ txt = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "raytracing-weeke
                      capture_output=True, text=True, check=True).stdout
 out = os.path.join(ROOT, "profiles", "sass")
 os.makedirs(out, exist_ok=True)
-keep = {"k_traverse_small", "k_shadow_small", "k_traverse_flat", "k_shadow_flat", "k_traverse", "k_shadow", "k_shade_all", "k_regen", "k_stream_fill_bvh", "k_stream_shade_bvh", "k_stream_advance", "k_karras",
+keep = {"k_traverse_small", "k_shadow_small", "k_traverse_flat", "k_shadow_flat", "k_traverse", "k_shadow", "k_shade_all", "k_regen", "k_stream_fill_bvh", "k_stream_shade_bvh", "k_stream_advance", "k_tail_small", "k_tail_flush", "k_karras",
         "k_refit", "k_sort_scatter", "k_morton", "k_prim_aabb", "k_tonemap", "k_trace"}
 index = []
 for p in re.split(r"\n\s*Function : ", txt)[1:]:
