@@ -134,6 +134,11 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "waves")) {
         if (value < 0 || value > rtw_ctx::kMaxWaves) return fail(c, RTW_ERR_INVALID, "waves out of range [0, 4] (0 = auto)");
         c->opt_waves = (int)value;
+    } else if (!strcmp(name, "node_min") || !strcmp(name, "prim_min")) {
+        if (value < 0 || value > 32) return fail(c, RTW_ERR_INVALID, "vote threshold out of range [0, 32]");
+        if (name[0] == 'n') c->opt_node_min = (int)value;
+        else c->opt_prim_min = (int)value;
+        c->cfg.node_min = c->opt_node_min; c->cfg.prim_min = c->opt_prim_min;
     } else if (!strcmp(name, "tail_paths")) {
         if (value < 0 || value > (1 << 22)) return fail(c, RTW_ERR_INVALID, "tail_paths out of range [0, 2^22]");
         c->opt_tail_paths = (int)value;
@@ -509,6 +514,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     }
     c->cfg.class_mask = c->class_mask;
     c->cfg.step_nodes = c->opt_step_nodes; c->cfg.step_prims = c->opt_step_prims; c->cfg.min_active = c->opt_min_active;
+    c->cfg.node_min = c->opt_node_min; c->cfg.prim_min = c->opt_prim_min;
     if (sc.root & RTW_REF_LEAF) {   // one leaf range: every ray does the same walk, nothing to rebalance
         c->cfg.step_nodes = 1; c->cfg.step_prims = RTW_MAX_LEAF_SIZE; c->cfg.min_active = 0;   // static mode
     }

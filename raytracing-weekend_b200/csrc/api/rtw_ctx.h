@@ -68,6 +68,7 @@ struct rtw_ctx {
     int opt_stagger = 0;             // odd waves start half an iteration after their even neighbour (measured slower)
     int opt_lockstep = 0;            // iteration i of every wave starts when all waves have finished iteration i - 1 (measured slower)
     int opt_tail_paths = 131072;     // slot pool: below this many paths alive (none left to start) one launch runs them to their end; 0 = off
+    int opt_node_min = 0, opt_prim_min = 0;   // walkers: warp-vote thresholds of the inner loops (0 = plain step)
     int opt_profile = 0;
     int opt_lag = 3;
 

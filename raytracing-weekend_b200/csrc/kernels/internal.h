@@ -55,6 +55,7 @@ struct LaunchCfg {
     uint32_t class_mask;    // which shading queues the scene can populate
     bool has_shadow;        // scene has lights → NEE stage runs
     int step_nodes, step_prims, min_active;   // persistent traversal: step bounds, refill threshold
+    int node_min, prim_min;                   // persistent traversal: warp-vote thresholds of the inner loops (0 = plain step)
     int shade_ctas;         // k_shade_all variant: resident CTAs per SM its registers are held to (2, 3 or 4)
     bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
     bool stream;            // streaming wavefront (kernels/stream.cu) instead of the slot pool (kernels/wavefront.cu)

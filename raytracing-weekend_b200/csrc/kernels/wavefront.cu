@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(kBlock) k_regen(const DScene sc, const DWave w
 // walk of the warp: ncu measured 8.3 of 32 lanes active on the Book-2 scene before this.
 struct WalkCfg {
     int step_nodes, step_prims, min_active;
+    int node_min, prim_min;   // > 0: inner loops under a warp vote (Walker::step_voted)
     // min_active <= 0: static mode — every ray does the same walk (the scene is one leaf range), so
     // warp k simply takes items 32k.., 32(k + #warps).. and no work counter is touched
 };
@@ -259,8 +260,9 @@ __device__ __forceinline__ void walk_persistent(const DScene& sc, const DWave* w
         // ---- walk until too few lanes are still busy (or, once the work is gone, until all are done) ----
         const int min_active = (!static_work && base + 32u <= total) ? wc.min_active : 1;
         do {
+            if (wc.node_min > 0) wk.step_voted(sc, s_top, stack, wc.step_nodes, wc.step_prims, wc.node_min, wc.prim_min);
+            else if (active) wk.step(sc, s_top, stack, wc.step_nodes, wc.step_prims);
             if (active) {
-                wk.step(sc, s_top, stack, wc.step_nodes, wc.step_prims);
                 if (wk.done) {
                     const int cls = job.store(item, wk.found, wk.tb, wk.lb);
                     if (kPush) { parked_cls = cls; parked_slot = item; }
@@ -653,7 +655,7 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (ev) cudaEventRecord(ev[1], s);
     if (cfg.small) k_traverse_small<<<cfg.grid_traverse, kBlock, 0, s>>>(sc, w, *cfg.small);
     else if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
-    else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
+    else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
     l++;
     if (cfg.mid_event) cudaEventRecord(cfg.mid_event, s);
     if (ev) cudaEventRecord(ev[2], s);
@@ -666,7 +668,7 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (cfg.has_shadow) {
         if (cfg.small) k_shadow_small<<<cfg.grid_shadow, kBlock, 0, s>>>(sc, w, *cfg.small);
         else if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
-        else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
+        else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
         l++;
     }
     if (ev) cudaEventRecord(ev[4], s);
@@ -699,7 +701,7 @@ cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg,
     }
     cudaError_t e = cudaMemsetAsync(work2, 0, 2 * sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    k_trace<<<grid, kBlock, cfg.smem_top, s>>>(sc, rays, n, hits, occluded, work2, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active});
+    k_trace<<<grid, kBlock, cfg.smem_top, s>>>(sc, rays, n, hits, occluded, work2, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
     if (launches) *launches += 1;
     return cudaGetLastError();
 }

@@ -262,7 +262,10 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
                      {"stream": 1, "walker": 0, "small": 1}, {"stream": 1, "walker": 0, "small": 0},
                      {"stream": 1, "walker": 0, "small": 0, "shade_ctas": 2}, {"stream": 1, "walker": 0, "small": 1, "shade_ctas": 4},
                      {"stream": 0, "shade_ctas": 3, "walker": 1}, {"walker": 1, "step_nodes": 1, "step_prims": 1, "min_active": 31},
-                     {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1}):
+                     {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1},
+                     {"walker": 1, "step_nodes": 16, "step_prims": 8, "min_active": 22, "node_min": 8, "prim_min": 4},
+                     {"walker": 1, "step_nodes": 5, "step_prims": 3, "min_active": 30, "node_min": 32, "prim_min": 32},
+                     {"walker": 1, "step_nodes": 16, "step_prims": 8, "min_active": 12, "node_min": 1, "prim_min": 0}):
             for k, v in opts.items():
                 director.set_option(k, v)
             director.createScene(sid)
@@ -278,5 +281,5 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             assert np.array_equal(hits, rh)
     finally:
         for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22,
-                     "tail_paths": 131072}.items():
+                     "tail_paths": 131072, "node_min": 0, "prim_min": 0}.items():
             director.set_option(k, v)
