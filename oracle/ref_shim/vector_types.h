@@ -1,0 +1,74 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  oracle/ref_shim: a CPU stand-in for the
+// headers the reference includes but does not ship (CUDA toolkit + OptiX SDK
+// 8.0.0), so that g++ can compile the reference's own sources where they lie
+// under /root/reference (recipe: oracle/Makefile, target `ref`).
+//
+// vector_types.h — the CUDA built-in vector types the reference uses, as plain
+// structs, plus the CUDA function-space keywords as no-ops.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cstring>
+#include <cmath>
+
+#ifndef __CUDACC__
+#define __host__
+#define __device__
+#define __global__
+#define __constant__
+#define __forceinline__ inline
+#define __align__(n) __attribute__((aligned(n)))
+#endif
+
+struct float2 { float x, y; };
+struct float3 { float x, y, z; };
+struct alignas(16) float4 { float x, y, z, w; };
+struct int2 { int x, y; };
+struct int3 { int x, y, z; };
+struct uint2 { unsigned int x, y; };
+struct uint3 { unsigned int x, y, z; };
+struct uchar4 { unsigned char x, y, z, w; };
+
+static inline float2 make_float2(float x, float y) { return float2{x, y}; }
+#ifdef REF_SHIM_MSVC_TEMPORARIES
+// The reference's host code binds temporaries to non-const references (scene/ioScene.h:942:
+// ioTransform::translate(make_float3(...)) against `translate(float3&)`), which MSVC accepts
+// and ISO C++ does not.  For the HOST translation units only (main.cpp, Director.cpp) the
+// three-argument make_float3 therefore hands out an lvalue from a per-thread ring; the values
+// are copied by every callee before the ring can wrap.
+static inline float3& make_float3(float x, float y, float z) {
+    static thread_local float3 ring[4096];
+    static thread_local unsigned next = 0;
+    float3& r = ring[next++ & 4095u];
+    r.x = x; r.y = y; r.z = z;
+    return r;
+}
+#else
+static inline float3 make_float3(float x, float y, float z) { return float3{x, y, z}; }
+#endif
+static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+static inline int2 make_int2(int x, int y) { return int2{x, y}; }
+static inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
+static inline uint3 make_uint3(unsigned x, unsigned y, unsigned z) { return uint3{x, y, z}; }
+
+// CUDA device intrinsics the reference uses to pass floats through OptiX attribute registers.
+static inline float __int_as_float(int v) { float f; std::memcpy(&f, &v, 4); return f; }
+static inline float __uint_as_float(unsigned v) { float f; std::memcpy(&f, &v, 4); return f; }
+static inline int __float_as_int(float f) { int v; std::memcpy(&v, &f, 4); return v; }
+static inline unsigned __float_as_uint(float f) { unsigned v; std::memcpy(&v, &f, 4); return v; }
+
+#ifdef REF_SHIM_LTR_ARGS
+// The reference draws several random numbers inside ONE argument list
+// (lib/sampling.cuh:30 `make_float3(rnd(seed), rnd(seed), rnd(seed))`, pdf/rectPdf.cu:128-130,
+// 150-152,174-176).  C++ leaves the order of evaluation of function arguments unspecified (g++
+// goes right to left, nvcc's choice is not observable here), so the reference's stream is not
+// a function of its source at these sites.  For the DEVICE translation units
+// the three-argument make_float3 is therefore spelled as a braced initialiser, whose clauses
+// C++ evaluates strictly left to right — the order oracle/oracle.cpp states.
+static inline float3 ref_make_float3_3(float x, float y, float z) { return float3{x, y, z}; }
+#define REF_MF3_PICK(_1, _2, _3, NAME, ...) NAME
+#define REF_MF3_3(a, b, c) (float3{(float)(a), (float)(b), (float)(c)})
+#define REF_MF3_2(a, b) ref_make_float3_bad_arity(a, b)
+#define REF_MF3_1(a) ref_make_float3_1(a)
+#define make_float3(...) REF_MF3_PICK(__VA_ARGS__, REF_MF3_3, REF_MF3_2, REF_MF3_1)(__VA_ARGS__)
+#endif

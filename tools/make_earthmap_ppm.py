@@ -1,23 +1,28 @@
 #!/usr/bin/env python3
-"""Decode the reference's earth-map JPEG into a binary PPM (P6) the C++ scene
-builder can read without a JPEG decoder.
+"""Decode the reference's earth-map JPEG into a binary PPM (P6) the C++ scene builder can
+read without a JPEG decoder.
 
-The reference decodes assets/earthmap.jpg with stb_image at run time
-(RestOfLife/texture/ioTexture.h:228-313).  /root/reference does not exist on the
-GPU box, and reference SOURCES (stb_image.h) are not copied into this repo, so
-the texels are baked once here with PIL (libjpeg-turbo; may differ from stb's
-IDCT by +-1 in some texels: documented in DESIGN.md, "image texture").
+The texels come from the REFERENCE'S OWN decode path: oracle/_ref/libref.so contains the
+reference's ioImageTexture (RestOfLife/texture/ioTexture.h:228-266) compiled where it lies
+together with its in-tree external/stb_image.h (`make -C oracle ref`); ref_load_image returns
+the RGBA8 array that code uploads (already flipped vertically, row 0 = bottom).  The PPM
+stores the rows top-down again — the scene builder applies the flip itself — so the file is
+byte for byte what stb_image decodes.  tests/test_ref_pin.py asserts the equality whenever
+/root/reference is present.
 
-Usage: python tools/make_earthmap_ppm.py [/root/reference/RestOfLife/assets/earthmap.jpg] [assets/earthmap.ppm]
+Usage: python tools/make_earthmap_ppm.py [assets/earthmap.ppm]
 """
+import os
 import sys
-from PIL import Image
 
-src = sys.argv[1] if len(sys.argv) > 1 else "/root/reference/RestOfLife/assets/earthmap.jpg"
-dst = sys.argv[2] if len(sys.argv) > 2 else "assets/earthmap.ppm"
-im = Image.open(src).convert("RGB")
-w, h = im.size
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import ref_py  # noqa: E402
+
+dst = sys.argv[1] if len(sys.argv) > 1 else "assets/earthmap.ppm"
+rgba = ref_py.load_image("assets/earthmap.jpg")
+h, w = rgba.shape[:2]
+rgb = rgba[::-1, :, :3]
 with open(dst, "wb") as f:
     f.write(b"P6\n%d %d\n255\n" % (w, h))
-    f.write(im.tobytes())
+    f.write(rgb.tobytes())
 print("wrote %s: %dx%d" % (dst, w, h))
