@@ -350,7 +350,8 @@ RTW_HD void hit_attributes(const DScene& sc, uint32_t leaf, const RayW& r, float
         }
         float3 n = (point - c) / a.w;
         h.normal = normal_to_world(n);
-        if (want_uv) get_sphere_uv(n, h.u, h.v);
+        // geometry/sphere.cu:66-69: get_sphere_uv takes the WORLD-space shading normal
+        if (want_uv) get_sphere_uv(h.normal, h.u, h.v);
     } else if (type == RTW_PRIM_RECT_X || type == RTW_PRIM_RECT_Y || type == RTW_PRIM_RECT_Z) {
         float pa, pb;
         float3 n;
