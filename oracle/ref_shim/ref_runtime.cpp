@@ -409,6 +409,7 @@ OptixResult optixLaunch(OptixPipeline, CUstream, CUdeviceptr params, size_t para
     g_sbt = *sbt;
     g_launches.fetch_add(1);
     const ProgramGroup* rg = record_pg(sbt->raygenRecord, 0, 0);
+    if (std::getenv("REF_SKIP_LAUNCH")) return OPTIX_SUCCESS;   // CLI tests: parse, build the scene, print a black frame
     int nt = g_threads;
     if (nt <= 0) { const char* e = std::getenv("REF_THREADS"); nt = e ? std::atoi(e) : (int)std::thread::hardware_concurrency(); }
     if (nt <= 0) nt = 1;

@@ -167,29 +167,9 @@ extern "C" int rtw_get_stats(rtw_ctx* c, rtw_stats* out) {
 // Scene upload: flat tables of Director::initLaunchParams / createSBT
 // (Director.cpp:483-553, 659-848) without the per-record cudaMalloc churn.
 // ---------------------------------------------------------------------------
+const char* rtw_internal_validate_desc(const rtw_scene_desc* d);   // host/scene_builder.cpp: every index and enumeration a kernel follows
 static int validate_scene(rtw_ctx* c, const rtw_scene_desc* d) {
-    if (d->n_prims <= 0 || !d->prims) return fail(c, RTW_ERR_INVALID, "scene has no primitives");
-    if (d->n_prims > RTW_MAX_PRIMS) return fail(c, RTW_ERR_INVALID, "too many primitives (max 2^25)");
-    if (d->n_materials <= 0 || !d->materials) return fail(c, RTW_ERR_INVALID, "scene has no materials");
-    if (d->n_lights > RTW_MAX_LIGHTS) return fail(c, RTW_ERR_INVALID, "more than RTW_MAX_LIGHTS lights");
-    for (int i = 0; i < d->n_prims; i++) {
-        const rtw_prim& p = d->prims[i];
-        if (p.type < 0 || p.type >= RTW_PRIM_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad primitive type");
-        if (p.material < 0 || p.material >= d->n_materials) return fail(c, RTW_ERR_INVALID, "primitive material out of range");
-        if (p.transform >= d->n_transforms) return fail(c, RTW_ERR_INVALID, "primitive transform out of range");
-    }
-    for (int i = 0; i < d->n_materials; i++) {
-        const rtw_material& m = d->materials[i];
-        if (m.type < 0 || m.type >= RTW_MAT_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad material type");
-        if (m.texture >= d->n_textures) return fail(c, RTW_ERR_INVALID, "material texture out of range");
-    }
-    for (int i = 0; i < d->n_textures; i++) {
-        const rtw_texture& t = d->textures[i];
-        if (t.type < 0 || t.type >= RTW_TEX_TYPE_COUNT) return fail(c, RTW_ERR_INVALID, "bad texture type");
-        if (t.type == RTW_TEX_NOISE && (t.perlin < 0 || t.perlin >= d->n_perlin)) return fail(c, RTW_ERR_INVALID, "noise table out of range");
-        if (t.type == RTW_TEX_IMAGE && (t.image < 0 || t.image >= d->n_images)) return fail(c, RTW_ERR_INVALID, "image out of range");
-        if (t.type == RTW_TEX_CHECKER && (t.odd >= d->n_textures || t.even >= d->n_textures)) return fail(c, RTW_ERR_INVALID, "checker child out of range");
-    }
+    if (const char* why = rtw_internal_validate_desc(d)) return fail(c, RTW_ERR_INVALID, why);
     return RTW_OK;
 }
 

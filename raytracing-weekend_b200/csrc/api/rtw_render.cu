@@ -257,6 +257,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
 
 extern "C" int rtw_tonemap(rtw_ctx* c, int Nx, int Ny, int spp_total, const float* accum_dev, float* rgba_out_dev) {
     if (!c || Nx <= 0 || Ny <= 0 || spp_total <= 0 || !accum_dev || !rgba_out_dev) return RTW_ERR_INVALID;
+    if ((unsigned long long)Nx * (unsigned long long)Ny > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image size out of range");
     RTW_CUDA(c, cudaSetDevice(c->device));
     uint64_t l = 0;
     RTW_CUDA(c, launch_tonemap(c->stream, Nx * Ny, spp_total, reinterpret_cast<const float4*>(accum_dev),
@@ -270,6 +271,7 @@ extern "C" int rtw_render(rtw_ctx* c, int Nx, int Ny, int spp, int max_depth, fl
     if (!c) return RTW_ERR_INVALID;
     if (!rgba_out_host || spp <= 0 || Nx <= 0 || Ny <= 0) return fail(c, RTW_ERR_INVALID, "bad render arguments");
     RTW_CUDA(c, cudaSetDevice(c->device));
+    if (Nx <= 0 || Ny <= 0 || (unsigned long long)Nx * (unsigned long long)Ny > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image size out of range");
     const int npix = Nx * Ny;
     if (c->frame_pixels != npix) {
         if (c->d_accum) cudaFree(c->d_accum);

@@ -675,12 +675,24 @@ bool index_ok(int32_t i, int32_t n, bool may_be_none) { return (may_be_none && i
 const char* validate_desc(const rtw_scene_desc& d) {
     if (d.n_prims < 1 || d.n_prims > (1 << 25)) return "primitive count out of range [1, 2^25]";
     if (d.n_materials < 1) return "no materials";
-    if (d.n_lights > 8) return "more than 8 lights";
+    if (d.n_lights < 0 || d.n_lights > 8) return "light count out of range [0, 8]";
+    if (d.n_transforms < 0 || d.n_textures < 0 || d.n_perlin < 0 || d.n_images < 0) return "negative table size";
+    if (!d.prims || !d.materials || (d.n_transforms && !d.transforms) || (d.n_textures && !d.textures) || (d.n_perlin && !d.perlin) ||
+        (d.n_images && !d.images) || (d.n_lights && !d.lights))
+        return "table pointer missing";
     for (int i = 0; i < d.n_prims; i++) {
         const rtw_prim& p = d.prims[i];
         if (p.type < 0 || p.type >= RTW_PRIM_TYPE_COUNT) return "primitive type out of range";
         if (!index_ok(p.material, d.n_materials, false)) return "primitive material index out of range";
         if (!index_ok(p.transform, d.n_transforms, true)) return "primitive transform index out of range";
+        // A moving sphere's LBVH box covers its centres for gather times inside [time0, time1] (device/lbvh.h);
+        // moving_center() extrapolates outside, so the camera's shutter interval must lie inside the sphere's.
+        if (p.type == RTW_PRIM_MOVING_SPHERE && p.v[7] != p.v[8]) {
+            const float lo = p.v[7] < p.v[8] ? p.v[7] : p.v[8], hi = p.v[7] < p.v[8] ? p.v[8] : p.v[7];
+            const float c0 = d.camera.time0 < d.camera.time1 ? d.camera.time0 : d.camera.time1;
+            const float c1 = d.camera.time0 < d.camera.time1 ? d.camera.time1 : d.camera.time0;
+            if (!(c0 >= lo && c1 <= hi)) return "camera shutter interval outside a moving sphere's time range";
+        }
     }
     for (int i = 0; i < d.n_materials; i++) {
         const rtw_material& m = d.materials[i];
@@ -712,6 +724,9 @@ const char* validate_desc(const rtw_scene_desc& d) {
 }
 
 }  // namespace
+
+// the one strict validator, also behind rtw_upload_scene (api/rtw_api.cu)
+const char* rtw_internal_validate_desc(const rtw_scene_desc* d) { return d ? validate_desc(*d) : "null scene description"; }
 
 static std::string g_scene_io_error;
 extern "C" const char* rtw_scene_io_error(void) { return g_scene_io_error.c_str(); }

@@ -143,3 +143,40 @@ def test_sample_counts_that_do_not_divide_by_the_waves(director, orc):
     finally:
         director.set_option("waves", 0)
         director.set_option("pool_paths", 0)
+
+
+def test_upload_refuses_what_the_scene_file_loader_refuses(director, rtw):
+    """rtw_upload_scene runs the one strict validator (advisor r01): negative indices, a textured material
+    without a texture, nested checkers and a shutter interval outside a moving sphere's time range are
+    refused with RTW_ERR_INVALID instead of being followed by a kernel."""
+    import ctypes as C
+    import scene_kit
+    L = rtw.lib()
+
+    def upload(k):
+        return L.rtw_upload_scene(director._c, k.desc)
+
+    k = scene_kit.build(rtw, "instances")
+    assert upload(k) == rtw.RTW_OK
+    for mutate in ("transform", "texture", "checker", "shutter", "odd"):
+        k = scene_kit.build(rtw, "branches" if mutate in ("checker", "odd") else "instances")
+        d = k.desc.contents
+        if mutate == "transform":
+            d.prims[0].transform = -2
+        elif mutate == "texture":
+            d.materials[0].texture = -1            # lambertian without a texture
+        elif mutate == "checker":
+            chk = [i for i in range(d.n_textures) if d.textures[i].type == rtw.TEX_CHECKER][0]
+            d.textures[chk].even = chk             # nested checker
+        elif mutate == "odd":
+            chk = [i for i in range(d.n_textures) if d.textures[i].type == rtw.TEX_CHECKER][0]
+            d.textures[chk].odd = -3
+        else:
+            d.camera.time1 = 2.0                   # moving sphere is defined on [0, 1]
+        assert upload(k) == rtw.RTW_ERR_INVALID, mutate
+        assert L.rtw_last_error(director._c)
+    # an image of more than 2^31 pixels is refused before anything is sized
+    out = np.zeros(4, np.float32)
+    assert L.rtw_render(director._c, 70000, 70000, 1, 1, out.ctypes.data) == rtw.RTW_ERR_INVALID
+    director.init(32, 32, 1)
+    director.createScene(0)

@@ -102,6 +102,57 @@ def test_converged_image_relmse(director, orc):
     assert ok.mean() >= 0.995, ok.mean()
 
 
+def test_tier2_at_the_benchmark_config(director, rtw):
+    """BASELINE.json tier 2 at C2 itself: Cornell 600x600, the 1024 spp frame against a
+    65536 spp frame of DISJOINT samples.  The numbers are MEASURED and written to gpurun_out/tier2_c2.json;
+    asserted is what any correct implementation of the reference's estimator must show: the error falls like
+    1/spp (variance, not bias), and the ladder reaches the 1e-3 target at the sample count recorded."""
+    import importlib
+    import json
+    import os
+    torch = pytest.importorskip("torch")
+    tier2 = importlib.import_module("raytracing-weekend_b200.tier2")
+    director.init(600, 600, 1024)
+    director.createScene(0)
+    m = tier2.measure(director, torch, 600, 600)
+    e = {int(k): v for k, v in m["relmse"].items()}
+    # variance ~ 1/spp: each x4 in samples divides the relMSE by ~4 (the reference's own noise, 1/64 of the
+    # 1024 spp error, rides on top)
+    for a, b in ((256, 1024), (1024, 4096), (4096, 16384)):
+        ratio = (e[a] - m["noise_floor_two_halves_of_reference"] / 4) / max(e[b] - m["noise_floor_two_halves_of_reference"] / 4, 1e-12)
+        assert 2.5 <= ratio <= 6.0, (a, b, ratio, m)
+    assert e[16384] <= 1e-3 or m["noise_floor_two_halves_of_reference"] > 2e-3, m
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "tier2_c2.json"), "w") as f:
+        json.dump(m, f, indent=1)
+    print("tier2 C2:", json.dumps(m))
+
+
+def test_same_samples_at_the_shipped_defaults(director, orc):
+    """C2's production configuration: 600x600, 32 spp = 11.5 M paths, so the
+    auto rule picks two waves x 2^21 slots, lagged counters, the drain-tail launch — against the
+    oracle's 32 spp of the SAME samples."""
+    Nx = Ny = 600
+    spp = 32
+    director.init(Nx, Ny, spp)
+    director.createScene(0)
+    for name in ("pool_paths", "waves"):
+        director.set_option(name, 0)          # 0 = the library's own choice
+    director.set_option("tail_paths", 131072)  # the shipped default (api/rtw_ctx.h)
+    director.renderFrame(spp)
+    st = director.stats()
+    assert st["waves"] == 2 and st["pool_paths"] == 1 << 21, st
+    lin = director.linear()
+    o = orc.OracleScene(director.scene.desc, 13)
+    ref, c = o.render(Nx, Ny, spp, mode=0)
+    assert np.all(lin[..., 3] == spp)
+    r = ref[..., :3] / spp
+    assert relmse(lin[..., :3], r) <= RELMSE_SAME_SAMPLES
+    assert np.allclose(lin[..., :3], r, rtol=1e-5, atol=1e-6)
+    assert st["rays_closest"] == c["rays_closest"] and st["rays_shadow"] == c["rays_shadow"] and st["paths"] == c["paths"]
+
+
 def test_pool_size_and_lag_do_not_change_the_image(director, orc):
     Nx = Ny = 64
     director.init(Nx, Ny, 8)

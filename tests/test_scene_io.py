@@ -116,3 +116,18 @@ def test_cli_reads_and_writes_scene_files(tmp_path):
     subprocess.check_call([cli, "-s", "0", "-dx", "64", "-dy", "64", "-ns", "2", "-o", str(a), "-w", str(f)])
     subprocess.check_call([cli, "-f", str(f), "-dx", "64", "-dy", "64", "-ns", "2", "-o", str(b)])
     assert a.read_bytes() == b.read_bytes()
+
+
+def test_save_refuses_a_shutter_outside_a_moving_spheres_time_range(rtw, tmp_path):
+    import scene_kit
+    k = scene_kit.build(rtw, "instances")
+    L = rtw.lib()
+    assert L.rtw_scene_save(C.cast(k.desc, C.c_void_p), b"ok", str(tmp_path / "a.rtws").encode()) == rtw.RTW_OK
+    k.desc.contents.camera.time0 = -0.5
+    assert L.rtw_scene_save(C.cast(k.desc, C.c_void_p), b"bad", str(tmp_path / "b.rtws").encode()) == rtw.RTW_ERR_INVALID
+    assert b"shutter" in L.rtw_scene_io_error()
+    # the hand-built scenes survive the wire format byte for byte
+    t = rtw.Scene.load(tmp_path / "a.rtws")
+    assert t.desc.contents.n_prims == k.n_prims
+    t.save(tmp_path / "c.rtws")
+    assert (tmp_path / "a.rtws").read_bytes() == (tmp_path / "c.rtws").read_bytes()
