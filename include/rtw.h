@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RTW_ABI_VERSION 1
+#define RTW_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 #define RTW_OK             0
@@ -254,6 +254,12 @@ int  rtw_render(rtw_ctx* ctx, int Nx, int Ny, int spp, int max_depth,
 int  rtw_render_accum(rtw_ctx* ctx, int Nx, int Ny,
                       int sample_first, int sample_stride, int sample_count,
                       int max_depth, float* accum_dev);
+/* The same for an image TILE: only the rows [row_first, row_first + row_count) are rendered (all the
+ * samples named by sample_first/stride/count), into the FULL-SIZE accumulator accum_dev (Nx*Ny float4).
+ * A pixel's samples do not depend on the tile it is rendered in. */
+int  rtw_render_accum_rows(rtw_ctx* ctx, int Nx, int Ny, int row_first, int row_count,
+                           int sample_first, int sample_stride, int sample_count,
+                           int max_depth, float* accum_dev);
 /* out_dev[i] = (sqrt(accum.rgb / spp_total), 1)  (raygen/raygen.cu:144-158) */
 int  rtw_tonemap(rtw_ctx* ctx, int Nx, int Ny, int spp_total,
                  const float* accum_dev, float* rgba_out_dev);
@@ -264,6 +270,32 @@ int  rtw_get_linear(rtw_ctx* ctx, float* rgba_linear_mean_host, int n_floats);
  * shared memory), "profile" (per-stage event timing 0/1), "graph" (CUDA graph 0/1). */
 int  rtw_set_option(rtw_ctx* ctx, const char* name, int64_t value);
 int  rtw_get_stats(rtw_ctx* ctx, rtw_stats* out);
+
+/* ---- several GPUs of one box (SURVEY.md §8b `rtw_create(const int* devices, int n, ...)`, §8e) ----
+ * One context, one worker thread and one stream set per listed GPU; scene and LBVH are replicated.
+ * rtw_multi_render shards a frame by SAMPLE (GPU g renders samples k = g (mod G); one
+ * ncclReduce(sum, float, root 0) of the fp32 accumulators per frame) or by image TILE (GPU g renders the
+ * rows [g*Ny/G, (g+1)*Ny/G); ncclSend/ncclRecv of the row blocks to GPU 0).  Option "shard": 0 = auto
+ * (tiles for frames below 2^23 paths, samples otherwise), 1 = samples, 2 = tiles; every other option is
+ * forwarded to each context (rtw_set_option).  The image for any G equals the 1-GPU image up to the
+ * order of the fp32 additions (bit for bit in tile mode at 1 spp).  The reference is single-GPU
+ * (Director.cpp:971-986): these entry points replace the same Director calls as their 1-GPU twins.
+ * NCCL is looked up at run time; without it (or with one GPU listed twice) peer copies are used. */
+typedef struct rtw_multi rtw_multi;
+int  rtw_create_multi(const int* devices, int n, rtw_multi** out);
+int  rtw_multi_destroy(rtw_multi* m);
+const char* rtw_multi_last_error(const rtw_multi* m);
+int  rtw_multi_device_count(const rtw_multi* m);
+int  rtw_multi_uses_nccl(const rtw_multi* m);
+int  rtw_multi_set_option(rtw_multi* m, const char* name, int64_t value);
+int  rtw_multi_upload_scene(rtw_multi* m, const rtw_scene_desc* scene);
+int  rtw_multi_build_accel(rtw_multi* m);
+int  rtw_multi_render(rtw_multi* m, int Nx, int Ny, int spp, int max_depth, float* rgba_out_host);
+/* linear means of the last frame (w = sample count), as rtw_get_linear */
+int  rtw_multi_get_linear(rtw_multi* m, float* rgba_linear_mean_host, int n_floats, int spp);
+/* total: counters summed over the GPUs, render_ms = the slowest GPU; per_device: one rtw_stats per GPU
+ * (may be NULL); exchange_ms: device time of the per-frame reduce / gather; shard: 1 samples, 2 tiles */
+int  rtw_multi_get_stats(rtw_multi* m, rtw_stats* total, rtw_stats* per_device, double* exchange_ms, int* shard);
 
 /* ---- tier-1 test hooks ---------------------------- */
 /* BVH closest hit / any hit on a caller-supplied ray set (host arrays). */

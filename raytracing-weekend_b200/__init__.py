@@ -116,6 +116,9 @@ ABI_SYMBOLS = [
     "rtw_get_stats", "rtw_trace_closest", "rtw_trace_any", "rtw_rng_stream", "rtw_camera_rays", "rtw_bvh_info_get",
     "rtw_bvh_download", "rtw_sort_pairs", "rtw_scene_create", "rtw_scene_get_desc", "rtw_scene_description",
     "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval", "rtw_scene_save", "rtw_scene_load", "rtw_scene_io_error",
+    "rtw_render_accum_rows", "rtw_create_multi", "rtw_multi_destroy", "rtw_multi_last_error", "rtw_multi_device_count",
+    "rtw_multi_uses_nccl", "rtw_multi_set_option", "rtw_multi_upload_scene", "rtw_multi_build_accel", "rtw_multi_render",
+    "rtw_multi_get_linear", "rtw_multi_get_stats",
 ]
 
 _lib = None
@@ -166,6 +169,18 @@ def lib():
         "rtw_scene_load": (i32, [C.c_char_p, C.POINTER(vp)]),
         "rtw_scene_io_error": (C.c_char_p, []),
         "rtw_write_ppm": (i32, [C.c_char_p, i32, i32, vp]),
+        "rtw_render_accum_rows": (i32, [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+        "rtw_create_multi": (i32, [C.POINTER(i32), i32, C.POINTER(vp)]),
+        "rtw_multi_destroy": (i32, [vp]),
+        "rtw_multi_last_error": (C.c_char_p, [vp]),
+        "rtw_multi_device_count": (i32, [vp]),
+        "rtw_multi_uses_nccl": (i32, [vp]),
+        "rtw_multi_set_option": (i32, [vp, C.c_char_p, i64]),
+        "rtw_multi_upload_scene": (i32, [vp, C.POINTER(SceneDesc)]),
+        "rtw_multi_build_accel": (i32, [vp]),
+        "rtw_multi_render": (i32, [vp, i32, i32, i32, i32, vp]),
+        "rtw_multi_get_linear": (i32, [vp, vp, i32, i32]),
+        "rtw_multi_get_stats": (i32, [vp, C.POINTER(Stats), C.POINTER(Stats), C.POINTER(C.c_double), C.POINTER(i32)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -369,6 +384,78 @@ class Director:
         if self.scene is not None:
             self.scene.close()
             self.scene = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class MultiDirector:
+    """Several GPUs of one box behind the C-ABI (rtw_create_multi): the same call order as Director."""
+
+    def __init__(self, devices):
+        self._m = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        rc = lib().rtw_create_multi(arr, len(devices), C.byref(self._m))
+        if rc != RTW_OK:
+            raise RtwError("rtw_create_multi(%s) failed: %d (no CPU fallback)" % (list(devices), rc))
+        self.devices = list(devices)
+        self.Nx = self.Ny = self.Ns = 0
+        self.max_depth = 20
+        self.scene = None
+
+    def _check(self, rc, what):
+        if rc != RTW_OK:
+            raise RtwError("%s failed (%d): %s" % (what, rc, lib().rtw_multi_last_error(self._m).decode()))
+
+    def init(self, Nx, Ny, Ns):
+        self.Nx, self.Ny, self.Ns = Nx, Ny, Ns
+
+    def set_option(self, name, value):
+        self._check(lib().rtw_multi_set_option(self._m, name.encode(), int(value)), "rtw_multi_set_option(%s)" % name)
+
+    def upload(self, desc_ptr):
+        self._check(lib().rtw_multi_upload_scene(self._m, desc_ptr), "rtw_multi_upload_scene")
+        self._check(lib().rtw_multi_build_accel(self._m), "rtw_multi_build_accel")
+
+    def createScene(self, scene_number, asset_dir=None, n_stress_prims=0):
+        self.scene = Scene(scene_number, self.Nx, self.Ny, asset_dir, n_stress_prims)
+        self.upload(self.scene.desc)
+
+    def uses_nccl(self):
+        return bool(lib().rtw_multi_uses_nccl(self._m))
+
+    def renderFrame(self, spp=None, max_depth=None):
+        spp = self.Ns if spp is None else spp
+        out = np.empty((self.Ny, self.Nx, 4), dtype=np.float32)
+        depth = self.max_depth if max_depth is None else max_depth
+        self._check(lib().rtw_multi_render(self._m, self.Nx, self.Ny, spp, depth, _ptr(out)), "rtw_multi_render")
+        self._spp = spp
+        return out
+
+    def linear(self):
+        out = np.empty((self.Ny, self.Nx, 4), dtype=np.float32)
+        self._check(lib().rtw_multi_get_linear(self._m, _ptr(out), out.size, self._spp), "rtw_multi_get_linear")
+        return out
+
+    def stats(self):
+        tot = Stats()
+        per = (Stats * len(self.devices))()
+        ex = C.c_double(0)
+        sh = C.c_int(0)
+        self._check(lib().rtw_multi_get_stats(self._m, C.byref(tot), per, C.byref(ex), C.byref(sh)), "rtw_multi_get_stats")
+        d = {k: getattr(tot, k) for k, _ in Stats._fields_}
+        d["exchange_ms"] = ex.value
+        d["shard"] = {1: "samples", 2: "tiles"}.get(sh.value, "?")
+        d["per_device"] = [{k: getattr(p, k) for k, _ in Stats._fields_} for p in per]
+        return d
+
+    def destroy(self):
+        if self._m:
+            lib().rtw_multi_destroy(self._m)
+            self._m = C.c_void_p()
 
     def __del__(self):
         try:

@@ -53,14 +53,20 @@ static inline uint64_t u64_at(const uint32_t* words, int lo) {
 
 extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, int sample_stride, int sample_count,
                                 int max_depth, float* accum_dev) {
+    return rtw_render_accum_rows(c, Nx, Ny, 0, Ny, sample_first, sample_stride, sample_count, max_depth, accum_dev);
+}
+
+extern "C" int rtw_render_accum_rows(rtw_ctx* c, int Nx, int Ny, int row_first, int row_count, int sample_first, int sample_stride,
+                                     int sample_count, int max_depth, float* accum_dev) {
     if (!c) return RTW_ERR_INVALID;
     if (!c->accel_built) return fail(c, RTW_ERR_STATE, "render before rtw_build_accel");
     if (Nx <= 0 || Ny <= 0 || sample_count < 0 || sample_first < 0 || sample_stride < 0 || max_depth < 0 ||
-        max_depth > 255 || !accum_dev)
+        max_depth > 255 || !accum_dev || row_first < 0 || row_count < 0 || row_first + row_count > Ny)
         return fail(c, RTW_ERR_INVALID, "bad render arguments");
     RTW_CUDA(c, cudaSetDevice(c->device));
-    const unsigned long long npix = (unsigned long long)Nx * (unsigned long long)Ny;
-    if (npix > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image too large");
+    if ((unsigned long long)Nx * (unsigned long long)Ny > 0x7fffffffull) return fail(c, RTW_ERR_INVALID, "image too large");
+    const unsigned long long npix = (unsigned long long)Nx * (unsigned long long)row_count;   // pixels of this call's tile
+    const uint32_t pixel_first = (uint32_t)row_first * (uint32_t)Nx;
     const unsigned long long total = npix * (unsigned long long)sample_count;
 
     uint64_t launches = 0;
@@ -70,7 +76,7 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
     st.build_ms = build_ms;
     if (max_depth == 0 && total > 0) {
         RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));   // no ray is ever traced: black samples, counted
-        RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, reinterpret_cast<float4*>(accum_dev), &launches));
+        RTW_CUDA(c, launch_add_count(c->stream, (int)npix, sample_count, reinterpret_cast<float4*>(accum_dev) + pixel_first, &launches));
         RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
         RTW_CUDA(c, cudaStreamSynchronize(c->stream));
         float ms0 = 0.f;
@@ -115,6 +121,8 @@ extern "C" int rtw_render_accum(rtw_ctx* c, int Nx, int Ny, int sample_first, in
         w.accum = reinterpret_cast<float4*>(accum_dev);
         w.Nx = Nx;
         w.Ny = Ny;
+        w.pixel_first = pixel_first;
+        w.pixel_count = (uint32_t)npix;
         w.max_depth = max_depth;
         w.sample_first = sample_first + j * sample_stride;
         w.sample_stride = sample_stride * n_waves;

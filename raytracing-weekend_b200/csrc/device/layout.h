@@ -216,7 +216,10 @@ struct DWave {
     int Nx, Ny;
     int max_depth;
     int sample_first, sample_stride;
-    unsigned long long total;   // Nx*Ny*sample_count sample ordinals to issue
+    unsigned long long total;   // pixel_count*sample_count sample ordinals to issue
+    // Image tiles (multi-GPU row sharding, api/rtw_multi.cu): the call renders the pixels
+    // [pixel_first, pixel_first + pixel_count) of the Nx x Ny image — whole rows — into the full-size accumulator.
+    uint32_t pixel_first, pixel_count;
     // Sparse mode (the drain tail of a frame, when most slots are empty; set per iteration by the host):
     // the slots with a ray to trace are listed instead of found by scanning the pool.
     int parity;                 // iteration index & 1

@@ -63,8 +63,8 @@ struct NewPath {
     float4 rad;
 };
 RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long ordinal) {
-    const unsigned long long npix = (unsigned long long)w.Nx * (unsigned long long)w.Ny;
-    const uint32_t pixel = (uint32_t)(ordinal % npix);
+    const unsigned long long npix = (unsigned long long)w.pixel_count;     // the tile of this call (the whole image: Nx * Ny)
+    const uint32_t pixel = w.pixel_first + (uint32_t)(ordinal % npix);
     const uint32_t ki = (uint32_t)(ordinal / npix);
     const uint32_t k = (uint32_t)w.sample_first + ki * (uint32_t)w.sample_stride;
     const uint32_t x = pixel % (uint32_t)w.Nx, y = pixel / (uint32_t)w.Nx;

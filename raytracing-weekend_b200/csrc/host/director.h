@@ -20,18 +20,22 @@ public:
     void destroy();                                                              // Director.cpp:86
 
     void setDevice(int device) { m_device = device; }
+    void setGpuCount(int n) { m_gpus = n < 1 ? 1 : n; }   // > 1: rtw_create_multi over devices device .. device + n - 1
     void setAssetDir(const std::string& d) { m_assets = d; }
     const rtw_stats& stats() const { return m_stats; }
     const std::vector<float>& frame() const { return m_frame; }
 
 private:
     void check(int rc, const char* what);
+    void uploadScene();
     bool _verbose, _debug;
     int m_device = 0;
     int m_Nx = 0, m_Ny = 0, m_Ns = 0;
     int m_maxRayDepth = 20;   // Director.cpp:42 (Q9)
     std::string m_assets = "assets";
+    int m_gpus = 1;
     rtw_ctx* m_ctx = nullptr;
+    rtw_multi* m_multi = nullptr;
     rtw_scene* m_scene = nullptr;
     rtw_stats m_stats{};
     std::vector<float> m_frame;

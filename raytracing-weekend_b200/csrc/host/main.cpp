@@ -3,7 +3,7 @@
 //   -s N  -ns N  -dx Nx  -dy Ny  -h  -v  -g      PPM (P3) on stdout, timing on stderr.
 // Documented normalisations: Q1 `-ns N` really takes N samples per
 // pixel (the reference stores N and traces 1); Q2 `-s` accepts 0..4 (the reference's
-// range test only lets 4 through).  Additive flags: -o FILE, -d DEVICE, -a ASSET_DIR, -j (JSON stats).
+// range test only lets 4 through).  Additive flags: -o FILE, -d DEVICE, -gpus N, -a ASSET_DIR, -j (JSON stats).
 #include <chrono>
 #include <cstdio>
 #include <iostream>
@@ -50,6 +50,8 @@ int main(int argc, char* argv[]) {
 
     -o FILE        Write the PPM to FILE instead of stdout.
     -d N           CUDA device index (default 0).
+    -gpus N        Render on N GPUs of this box (devices d .. d+N-1): samples or image tiles are sharded,
+                   one NCCL reduce / gather per frame.
     -a DIR         Asset directory holding earthmap.ppm (default "assets").
     -j             Print one JSON line with render statistics on stderr.
     -f FILE        Render the scene stored in FILE (scene wire format) instead of scene -s N.
@@ -117,6 +119,9 @@ int main(int argc, char* argv[]) {
     int device = 0;
     const std::string& dev = cl_input.getCmdOption("-d");
     if (!dev.empty()) parse_int(dev, device);
+    int gpus = 1;
+    const std::string& ngpu = cl_input.getCmdOption("-gpus");
+    if (!ngpu.empty()) parse_int(ngpu, gpus);
     const std::string& out = cl_input.getCmdOption("-o");
     const std::string& assets = cl_input.getCmdOption("-a");
     const std::string& scene_in = cl_input.getCmdOption("-f");
@@ -124,6 +129,7 @@ int main(int argc, char* argv[]) {
 
     Director director(Qverbose, Qdebug);
     director.setDevice(device);
+    director.setGpuCount(gpus);
     if (!assets.empty()) director.setAssetDir(assets);
 
     auto start = std::chrono::system_clock::now();

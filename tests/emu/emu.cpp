@@ -294,6 +294,7 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
     w.P = P; w.Nx = Nx; w.Ny = Ny; w.max_depth = max_depth;
     w.sample_first = sample_first; w.sample_stride = sample_stride;
     w.total = (unsigned long long)Nx * Ny * sample_count;
+    w.pixel_first = 0; w.pixel_count = (uint32_t)(Nx * Ny);
     unsigned long long next = 0, rays = 0, shrays = 0, iters = 0;
     if (max_depth == 0) {   // k_add_count
         for (int i = 0; i < Nx * Ny; i++) accum[4 * i + 3] += (float)sample_count;
@@ -356,6 +357,7 @@ extern "C" void emu_camera_rays(const Emu* e, int Nx, int Ny, int sample, rtw_ra
     const int npix = Nx * Ny;
     DWave w{};
     w.P = npix; w.Nx = Nx; w.Ny = Ny; w.sample_first = sample; w.sample_stride = 0; w.total = npix;
+    w.pixel_first = 0; w.pixel_count = (uint32_t)npix;
     for (int i = 0; i < npix; i++) {
         const NewPath np = make_path(e->sc, w, (unsigned long long)i);
         rtw_ray& r = out[i];

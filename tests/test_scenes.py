@@ -130,7 +130,7 @@ def test_abi_exports_every_declared_symbol(rtw):
     L = rtw.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.rtw_abi_version() == 1
+    assert L.rtw_abi_version() == 2
 
 
 def test_abi_struct_sizes(rtw):
