@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--leaf-size", type=int, default=0)
     ap.add_argument("--opt", action="append", default=[], help="name=value passed to rtw_set_option (tuning runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-relmse", action="store_true", help="skip the tier-2 relMSE measurement (N=1 only; ~10 s of GPU time)")
     args = ap.parse_args()
     if (args.scene, args.nx, args.ny) != (SCENE, NX, NY):
         SCENE, NX, NY = args.scene, args.nx, args.ny

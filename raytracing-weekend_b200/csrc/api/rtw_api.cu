@@ -142,6 +142,11 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "tail_paths")) {
         if (value < 0 || value > (1 << 22)) return fail(c, RTW_ERR_INVALID, "tail_paths out of range [0, 2^22]");
         c->opt_tail_paths = (int)value;
+    } else if (!strcmp(name, "fuse_shadow")) {
+        if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "fuse_shadow out of range [-1, 1]");
+        c->opt_fuse_shadow = (int)value;
+        c->cfg.fuse_shadow = c->cfg.small && (value != 0);
+        if (c->accel_built) { cudaError_t e = wavefront_configure(c->scene, &c->cfg); if (e != cudaSuccess) return cuda_fail(c, e, "wavefront_configure"); }
     } else if (!strcmp(name, "lockstep")) {
         c->opt_lockstep = value ? 1 : 0;
     } else if (!strcmp(name, "stagger")) {
@@ -485,6 +490,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
             for (int k = 0; k < 3; k++) ss.w2o[3 * j + k] = xf[6 * j + k];
         c->cfg.small = &c->small;
     }
+    c->cfg.fuse_shadow = c->cfg.small && c->opt_fuse_shadow != 0;
     RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
     if (c->opt_grid_pct < 100) {
         int sms = 148;

@@ -69,6 +69,7 @@ struct rtw_ctx {
     int opt_lockstep = 0;            // iteration i of every wave starts when all waves have finished iteration i - 1 (measured slower)
     int opt_tail_paths = 131072;     // slot pool: below this many paths alive (none left to start) one launch runs them to their end; 0 = off
     int opt_node_min = 0, opt_prim_min = 0;   // walkers: warp-vote thresholds of the inner loops (0 = plain step)
+    int opt_fuse_shadow = -1;        // -1 = auto (on for by-value small scenes), 0 = shadow queue + k_shadow_small, 1 = NEE rays traced inside k_shade_all
     int opt_profile = 0;
     int opt_lag = 3;
 

@@ -163,6 +163,7 @@ struct ShadowOut {
     float tmax;
     float3 contrib;
     uint32_t seed;
+    float gather;     // PerRayData::gatherTime of the path (moving spheres)
 };
 
 // __closesthit__radiance (shaders/closehit.cu:45-121) / __miss__Program
@@ -257,6 +258,7 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
                 sh.tmax = ls.distance - 500 * 1.0e-7f;
                 sh.contrib = nee * throughput;  // added by the shadow stage iff unoccluded
                 sh.seed = seed;
+                sh.gather = rd.w;
             }
         }
     }

@@ -54,6 +54,7 @@ struct LaunchCfg {
     size_t smem_top;        // bytes of shared memory for the staged top nodes
     uint32_t class_mask;    // which shading queues the scene can populate
     bool has_shadow;        // scene has lights → NEE stage runs
+    bool fuse_shadow;       // small scenes: the shading kernel traces its NEE rays in place (no shadow queue, no k_shadow launch)
     int step_nodes, step_prims, min_active;   // persistent traversal: step bounds, refill threshold
     int node_min, prim_min;                   // persistent traversal: warp-vote thresholds of the inner loops (0 = plain step)
     int shade_ctas;         // k_shade_all variant: resident CTAs per SM its registers are held to (2, 3 or 4)

@@ -374,8 +374,14 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWav
 
 // ---------------------------------------------------------------------------
 // One 256-wide chunk [i0, i0 + 256) of shading queue kClass: every warp runs ONE BSDF.
-template <int kClass>
-__device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, uint32_t slot, uint32_t ahead) {
+// kFuse (small scenes, option fuse_shadow): the NEE shadow ray is traced HERE, against the by-value copy of the
+// scene, instead of travelling through the shadow queue to k_shadow_small — 96 B of DRAM traffic per NEE ray
+// (48 B written + 48 B read) and one launch per iteration less.  The any-hit walk is warp-uniform (every lane
+// walks the same 13 records; a lane without an NEE ray walks a null ray), the unoccluded contribution goes
+// into the slot's radiance record exactly as k_shadow_small would have added it, in the same order.
+template <int kClass, bool kFuse>
+__device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, uint32_t slot, uint32_t ahead, const SmallScene* ss,
+                                            uint32_t& n_shadow) {
     const uint32_t lane = threadIdx.x & 31u;
     ShadowOut sh;
     sh.emit = false;
@@ -387,8 +393,25 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
     // trace list) — reserve their space with ONE atomic round trip: lanes 0, 1, 2 each add one count.
     const bool survivor = w.trace_fill && slot != RTW_REF_NONE && !finished;
     const uint32_t m_regen = __ballot_sync(0xffffffffu, finished);
-    const uint32_t m_shadow = kClass == RTW_Q_LAMBERTIAN ? __ballot_sync(0xffffffffu, sh.emit) : 0u;
+    uint32_t m_shadow = kClass == RTW_Q_LAMBERTIAN ? __ballot_sync(0xffffffffu, sh.emit) : 0u;
     const uint32_t m_trace = w.trace_fill ? __ballot_sync(0xffffffffu, survivor) : 0u;
+    if (kFuse && kClass == RTW_Q_LAMBERTIAN && m_shadow != 0u) {
+        RayW r;   // traceOcclusion, shaders/closehit.cu:16-42,97-113: tmin 500e-7, ray time 0
+        r.o = f3(0.f); r.d = f3(1.f); r.tmin = 500 * 1.0e-7f; r.tmax = 0.f; r.time = 0.f; r.gather = 0.f; r.seed = 0u;
+        if (sh.emit) {
+            r.o = sh.o; r.d = sh.d; r.tmax = sh.tmax;
+            r.gather = sc.has_motion ? sh.gather : 0.f;
+            r.seed = sh.seed;
+        }
+        const bool occluded = small_any(*ss, r);
+        if (sh.emit && !occluded) {
+            float4 ra = w.rad[slot];
+            ra.x += sh.contrib.x; ra.y += sh.contrib.y; ra.z += sh.contrib.z;
+            w.rad[slot] = ra;
+        }
+        n_shadow += (uint32_t)__popc(m_shadow);   // every lane keeps the warp's count; lane 0 publishes it
+        m_shadow = 0u;
+    }
     if ((m_regen | m_shadow | m_trace) == 0u) return;
     const uint32_t mine = lane == 0 ? m_regen : (lane == 1 ? m_shadow : m_trace);
     const int counter = lane == 0 ? RTW_C_QUEUE0 + RTW_Q_REGEN : (lane == 1 ? RTW_C_SHADOW : RTW_C_TRACE0 + (w.parity ^ 1));
@@ -400,7 +423,7 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
     const uint32_t below = (1u << lane) - 1u;
     if (finished) w.queue[(size_t)RTW_Q_REGEN * w.P + b_regen + __popc(m_regen & below)] = slot;
     if (survivor) w.queue[(size_t)RTW_Q_TRACE * w.P + b_trace + __popc(m_trace & below)] = slot;
-    if (kClass == RTW_Q_LAMBERTIAN && sh.emit) {
+    if (!kFuse && kClass == RTW_Q_LAMBERTIAN && sh.emit) {
         const uint32_t pos = b_shadow + __popc(m_shadow & below);
         w.sh_o[pos] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmax);
         w.sh_d[pos] = make_float4(sh.d.x, sh.d.y, sh.d.z, __uint_as_float(slot));
@@ -415,8 +438,8 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
 // with the machine mostly idle.
 // kCtas = resident CTAs per SM the register allocation is held to (option `shade_ctas`): 2 → 95 registers,
 // 3 → 80, 4 → 64; the kernel is bound by memory latency, so warps in flight are what it is short of.
-template <int kCtas>
-__global__ void __launch_bounds__(kBlock, kCtas) k_shade_all(const DScene sc, const DWave w, uint32_t class_mask) {
+template <bool kFuse>
+__device__ __forceinline__ void shade_all_body(const DScene& sc, const DWave& w, uint32_t class_mask, const SmallScene* ss) {
     // queue lengths and the first chunk number of every class: shared memory, not registers (the kernel is
     // register-bound: 128 with the tables in registers and spills, see profiles/sass/INDEX.md)
     __shared__ uint32_t s_n[RTW_Q_COUNT], s_first[RTW_Q_COUNT + 1];
@@ -450,17 +473,19 @@ __global__ void __launch_bounds__(kBlock, kCtas) k_shade_all(const DScene sc, co
     // inside the chunk, `ahead2` is requested now — so the prefetch never waits for its own index load.
     uint32_t slot = entry(blockIdx.x);
     uint32_t ahead = entry(blockIdx.x + gridDim.x);
+    uint32_t n_shadow = 0;   // kFuse: NEE rays this warp traced in place
     for (uint32_t v = blockIdx.x; v < chunks; v += gridDim.x) {
         const uint32_t ahead2 = entry(v + 2 * gridDim.x);
         const int c = class_of(v);
-        if (c == RTW_Q_LAMBERTIAN) shade_chunk<RTW_Q_LAMBERTIAN>(sc, w, slot, ahead);
-        else if (c == RTW_Q_METAL) shade_chunk<RTW_Q_METAL>(sc, w, slot, ahead);
-        else if (c == RTW_Q_DIELECTRIC) shade_chunk<RTW_Q_DIELECTRIC>(sc, w, slot, ahead);
-        else if (c == RTW_Q_ISOTROPIC) shade_chunk<RTW_Q_ISOTROPIC>(sc, w, slot, ahead);
-        else shade_chunk<RTW_Q_TERMINAL>(sc, w, slot, ahead);
+        if (c == RTW_Q_LAMBERTIAN) shade_chunk<RTW_Q_LAMBERTIAN, kFuse>(sc, w, slot, ahead, ss, n_shadow);
+        else if (c == RTW_Q_METAL) shade_chunk<RTW_Q_METAL, kFuse>(sc, w, slot, ahead, ss, n_shadow);
+        else if (c == RTW_Q_DIELECTRIC) shade_chunk<RTW_Q_DIELECTRIC, kFuse>(sc, w, slot, ahead, ss, n_shadow);
+        else if (c == RTW_Q_ISOTROPIC) shade_chunk<RTW_Q_ISOTROPIC, kFuse>(sc, w, slot, ahead, ss, n_shadow);
+        else shade_chunk<RTW_Q_TERMINAL, kFuse>(sc, w, slot, ahead, ss, n_shadow);
         slot = ahead;
         ahead = ahead2;
     }
+    if (kFuse && (threadIdx.x & 31u) == 0u && n_shadow) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n_shadow);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // ray statistics of this iteration: every queued slot was one closest-hit ray (the shadow
         // rays are counted by k_shadow, once the shadow queue is complete)
@@ -469,6 +494,16 @@ __global__ void __launch_bounds__(kBlock, kCtas) k_shade_all(const DScene sc, co
         atomic_add_u64(w.counters + RTW_C_RAYS_LO, rays);
         w.counters[RTW_C_ALIVE] = (uint32_t)rays;   // 0 ⇒ nothing left in flight: the host stops iterating
     }
+}
+template <int kCtas>
+__global__ void __launch_bounds__(kBlock, kCtas) k_shade_all(const DScene sc, const DWave w, uint32_t class_mask) {
+    shade_all_body<false>(sc, w, class_mask, nullptr);
+}
+// small scenes with NEE: the shadow rays are traced in place (shade_chunk, kFuse)
+template <int kCtas>
+__global__ void __launch_bounds__(kBlock, kCtas) k_shade_all_fused(const DScene sc, const DWave w, uint32_t class_mask,
+                                                                    const __grid_constant__ SmallScene ss) {
+    shade_all_body<true>(sc, w, class_mask, &ss);
 }
 
 // ---------------------------------------------------------------------------
@@ -635,8 +670,12 @@ cudaError_t wavefront_configure(const DScene& sc, LaunchCfg* cfg) {
         cfg->grid_traverse = resident_grid(k_traverse, cfg->smem_top, sms);
         cfg->grid_shadow = resident_grid(k_shadow, cfg->smem_top, sms);
     }
-    cfg->grid_shade = cfg->shade_ctas == 2 ? resident_grid(k_shade_all<2>, 0, sms)
-                    : cfg->shade_ctas == 4 ? resident_grid(k_shade_all<4>, 0, sms) : resident_grid(k_shade_all<3>, 0, sms);
+    if (cfg->fuse_shadow && cfg->small)
+        cfg->grid_shade = cfg->shade_ctas == 2 ? resident_grid(k_shade_all_fused<2>, 0, sms)
+                        : cfg->shade_ctas == 4 ? resident_grid(k_shade_all_fused<4>, 0, sms) : resident_grid(k_shade_all_fused<3>, 0, sms);
+    else
+        cfg->grid_shade = cfg->shade_ctas == 2 ? resident_grid(k_shade_all<2>, 0, sms)
+                        : cfg->shade_ctas == 4 ? resident_grid(k_shade_all<4>, 0, sms) : resident_grid(k_shade_all<3>, 0, sms);
     return cudaSuccess;
 }
 
@@ -660,12 +699,17 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (cfg.mid_event) cudaEventRecord(cfg.mid_event, s);
     if (ev) cudaEventRecord(ev[2], s);
     const uint32_t classes = cfg.class_mask | (1u << RTW_Q_TERMINAL);
-    if (cfg.shade_ctas == 2) k_shade_all<2><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
+    const bool fused = cfg.fuse_shadow && cfg.small && cfg.has_shadow;
+    if (fused) {
+        if (cfg.shade_ctas == 2) k_shade_all_fused<2><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes, *cfg.small);
+        else if (cfg.shade_ctas == 4) k_shade_all_fused<4><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes, *cfg.small);
+        else k_shade_all_fused<3><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes, *cfg.small);
+    } else if (cfg.shade_ctas == 2) k_shade_all<2><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
     else if (cfg.shade_ctas == 4) k_shade_all<4><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
     else k_shade_all<3><<<cfg.grid_shade, kBlock, 0, s>>>(sc, w, classes);
     l++;
     if (ev) cudaEventRecord(ev[3], s);
-    if (cfg.has_shadow) {
+    if (cfg.has_shadow && !fused) {
         if (cfg.small) k_shadow_small<<<cfg.grid_shadow, kBlock, 0, s>>>(sc, w, *cfg.small);
         else if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
         else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
