@@ -211,6 +211,8 @@ typedef struct rtw_stats {
     double   logic_ms;          /* device time inside k_logic, ditto            */
     uint64_t waves;             /* concurrent pools the last render was dealt to */
     uint64_t pool_paths;        /* path slots per pool                          */
+    uint64_t nee_unoccluded;    /* NEE contributions added (shadow rays that reached the light); 0 where the variant does not count them */
+    uint64_t stack_overflows;   /* traversal-stack pushes that found the stack full (must be 0: the render returns RTW_ERR_STATE otherwise) */
 } rtw_stats;
 
 typedef struct rtw_bvh_info {

@@ -55,6 +55,12 @@ def lib(dm=True):
     L.ref_load_image.restype = i32
     L.ref_load_image.argtypes = [C.c_char_p, C.c_char_p, vp, vp, vp, i32]
     L.ref_run_main.restype = i32
+    L.ref_open.restype = i32
+    L.ref_open.argtypes = [i32, i32, i32, C.c_char_p, i32]
+    L.ref_launch.restype = i32
+    L.ref_launch.argtypes = [i32]
+    L.ref_frame.restype = i32
+    L.ref_frame.argtypes = [vp]
     _libs[dm] = L
     return L
 
@@ -120,3 +126,28 @@ def load_image(file="assets/earthmap.jpg", asset_root=REF_ROOT, dm=True):
     if rc != 0:
         raise RuntimeError("ref_load_image failed")
     return out
+
+
+class Session:
+    """Director::init + createScene once, renderFrame() on demand (bench.py's reference arm).  Every launch is
+    the reference's one and only frame: 1 spp with the seeds of sample 0 (raygen/raygen.cu:129)."""
+
+    def __init__(self, scene, Nx, Ny, dm=False, threads=0, q23_normalise=False, asset_root=REF_ROOT):
+        self.L = lib(dm)
+        self.Nx, self.Ny = Nx, Ny
+        self.L.ref_set_threads(threads)
+        self.L.ref_set_q23_normalise(1 if q23_normalise else 0)
+        root = asset_root if (asset_root and os.path.isdir(asset_root)) else None
+        if self.L.ref_open(scene, Nx, Ny, root.encode() if root else None, 1) != 0:
+            raise RuntimeError("ref_open(%d) failed: %s" % (scene, self.L.ref_last_error().decode()))
+
+    def launch(self, n=1):
+        t0 = self.L.ref_traversal_count()
+        if self.L.ref_launch(n) != 0:
+            raise RuntimeError("ref_launch failed: %s" % self.L.ref_last_error().decode())
+        return int(self.L.ref_traversal_count() - t0)       # optixTraverse calls (closest-hit + shadow rays)
+
+    def frame(self):
+        out = np.zeros((self.Ny, self.Nx, 4), np.float32)
+        self.L.ref_frame(_ptr(out))
+        return out

@@ -308,6 +308,41 @@ int ref_render_scene(int scene, int Nx, int Ny, int launches, const char* asset_
     }
 }
 
+/* A session for timing (bench.py's reference arm): Director::init + createScene once, then renderFrame()
+ * as often as asked.  Every launch renders the same 1 spp frame (raygen/raygen.cu:129 seeds sample 0). */
+static Director* g_session = nullptr;
+static int g_session_nx = 0, g_session_ny = 0;
+int ref_open(int scene, int Nx, int Ny, const char* asset_root, int quiet) {
+    try {
+        Cwd cwd(asset_root);
+        QuietStderr q(quiet != 0);
+        g_session = new Director(false, false);
+        g_session->init(Nx, Ny, 1);
+        g_session->createScene(scene);
+        g_session_nx = Nx; g_session_ny = Ny;
+        return 0;
+    } catch (const std::exception& e) {
+        g_flat.error = e.what();
+        g_session = nullptr;
+        return 1;
+    }
+}
+int ref_launch(int launches) {
+    if (!g_session) return 1;
+    try {
+        for (int i = 0; i < launches; i++) g_session->renderFrame();
+        return 0;
+    } catch (const std::exception& e) {
+        g_flat.error = e.what();
+        return 1;
+    }
+}
+int ref_frame(float* rgba_out) {
+    if (!g_session || !rgba_out) return 1;
+    memcpy(rgba_out, Parameter.frame_buffer, sizeof(float4) * (size_t)g_session_nx * g_session_ny);
+    return 0;
+}
+
 /* The scene the last ref_render_scene launch ran on, as an rtw_scene_desc (owned by the library,
  * valid until the next call).  prims[i] = instance i of the IAS; prims[i].material = its instanceId. */
 const rtw_scene_desc* ref_scene_desc() { return g_flat.prims.empty() ? nullptr : &g_flat.desc; }

@@ -96,7 +96,8 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("iterations", C.c_uint64), ("render_ms", C.c_double),
                 ("build_ms", C.c_double), ("traverse_ms", C.c_double), ("shadow_ms", C.c_double),
-                ("shade_ms", C.c_double), ("logic_ms", C.c_double), ("waves", C.c_uint64), ("pool_paths", C.c_uint64)]
+                ("shade_ms", C.c_double), ("logic_ms", C.c_double), ("waves", C.c_uint64), ("pool_paths", C.c_uint64),
+                ("nee_unoccluded", C.c_uint64), ("stack_overflows", C.c_uint64)]
 
 
 class BvhInfo(C.Structure):

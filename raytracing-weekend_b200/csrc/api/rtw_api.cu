@@ -57,6 +57,8 @@ extern "C" int rtw_create(int device, rtw_ctx** out) {
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_end);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&c->d_overflow), sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(c->d_overflow, 0, sizeof(uint32_t));
     if (e != cudaSuccess) {
         g_create_error = std::string("context setup: ") + cudaGetErrorString(e);
         delete c;
@@ -92,6 +94,7 @@ extern "C" int rtw_destroy(rtw_ctx* c) {
     for (auto& e : c->prof_events) if (e) cudaEventDestroy(e);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->d_overflow) cudaFree(c->d_overflow);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return RTW_OK;
@@ -145,7 +148,7 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "fuse_shadow")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "fuse_shadow out of range [-1, 1]");
         c->opt_fuse_shadow = (int)value;
-        c->cfg.fuse_shadow = c->cfg.small && (value != 0);
+        c->cfg.fuse_shadow = c->cfg.small && (value > 0);
         if (c->accel_built) { cudaError_t e = wavefront_configure(c->scene, &c->cfg); if (e != cudaSuccess) return cuda_fail(c, e, "wavefront_configure"); }
     } else if (!strcmp(name, "lockstep")) {
         c->opt_lockstep = value ? 1 : 0;
@@ -188,6 +191,7 @@ extern "C" int rtw_upload_scene(rtw_ctx* c, const rtw_scene_desc* d) {
     c->scene_loaded = false;
     c->accel_built = false;
     c->scene = DScene{};
+    c->scene.overflow = c->d_overflow;
     c->build = BuildBuffers{};
     auto& pool = c->scene_allocs;
     const int n = d->n_prims;
@@ -490,7 +494,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
             for (int k = 0; k < 3; k++) ss.w2o[3 * j + k] = xf[6 * j + k];
         c->cfg.small = &c->small;
     }
-    c->cfg.fuse_shadow = c->cfg.small && c->opt_fuse_shadow != 0;
+    c->cfg.fuse_shadow = c->cfg.small && c->opt_fuse_shadow > 0;
     RTW_CUDA(c, wavefront_configure(sc, &c->cfg));
     if (c->opt_grid_pct < 100) {
         int sms = 148;

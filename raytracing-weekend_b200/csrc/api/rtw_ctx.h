@@ -69,9 +69,13 @@ struct rtw_ctx {
     int opt_lockstep = 0;            // iteration i of every wave starts when all waves have finished iteration i - 1 (measured slower)
     int opt_tail_paths = 131072;     // slot pool: below this many paths alive (none left to start) one launch runs them to their end; 0 = off
     int opt_node_min = 0, opt_prim_min = 0;   // walkers: warp-vote thresholds of the inner loops (0 = plain step)
-    int opt_fuse_shadow = -1;        // -1 = auto (on for by-value small scenes), 0 = shadow queue + k_shadow_small, 1 = NEE rays traced inside k_shade_all
+    int opt_fuse_shadow = 0;         // 1 = by-value small scenes trace their NEE rays inside k_shade_all (no shadow queue, no k_shadow_small launch).
+                                     // Measured on the B200, C2 (profiles/r02/r02c_fuse_shadow.md): 2656 Mpaths/s fused against 3057 with the queue —
+                                     // the separate shadow launch is what the OTHER wave's DRAM-bound shading launch overlaps with; default off
     int opt_profile = 0;
     int opt_lag = 3;
+
+    uint32_t* d_overflow = nullptr;  // DScene::overflow: traversal-stack pushes that found the stack full
 
     rtw_stats stats{};
 };
@@ -91,6 +95,19 @@ inline int cuda_fail(rtw_ctx* c, cudaError_t e, const char* what) {
         cudaError_t e__ = (call);                                     \
         if (e__ != cudaSuccess) return rtw::cuda_fail((c), e__, #call); \
     } while (0)
+
+// After a render / trace call: a traversal that ran out of stack dropped a subtree — fail loudly instead of
+// returning a wrong answer (the word is cleared for the next call).
+inline int check_overflow(rtw_ctx* c, uint64_t* count_out) {
+    uint32_t v = 0;
+    if (!c->d_overflow) return RTW_OK;
+    cudaError_t e = cudaMemcpy(&v, c->d_overflow, sizeof(v), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return cuda_fail(c, e, "cudaMemcpy(overflow word)");
+    if (count_out) *count_out = v;
+    if (v == 0) return RTW_OK;
+    cudaMemset(c->d_overflow, 0, sizeof(v));
+    return fail(c, RTW_ERR_STATE, "traversal stack overflow: " + std::to_string(v) + " pushes dropped (hierarchy deeper than the stack)");
+}
 
 template <class T>
 inline cudaError_t dalloc(std::vector<void*>& pool, T** out, size_t count) {

@@ -34,7 +34,7 @@ static int trace_common(rtw_ctx* c, const rtw_ray* rays, int n, rtw_hit* hits, i
     if (hits) RTW_CUDA(c, cudaMemcpyAsync(hits, d_hits, sizeof(rtw_hit) * n, cudaMemcpyDeviceToHost, c->stream));
     if (occ) RTW_CUDA(c, cudaMemcpyAsync(occ, d_occ, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
     RTW_CUDA(c, cudaStreamSynchronize(c->stream));
-    return RTW_OK;
+    return check_overflow(c, nullptr);
 }
 
 extern "C" int rtw_trace_closest(rtw_ctx* c, const rtw_ray* rays, int n, rtw_hit* hits) {

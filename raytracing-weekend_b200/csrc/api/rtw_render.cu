@@ -241,6 +241,7 @@ extern "C" int rtw_render_accum_rows(rtw_ctx* c, int Nx, int Ny, int row_first, 
     for (int j = 0; j < n_waves; j++) {
         st.rays_closest += u64_at(c->waves[j].h_counters, RTW_C_RAYS_LO);
         st.rays_shadow += u64_at(c->waves[j].h_counters, RTW_C_SHRAYS_LO);
+        st.nee_unoccluded += u64_at(c->waves[j].h_counters, RTW_C_UNOCC_LO);
         iterations += run[j].iter;
     }
     st.kernel_launches = launches;
@@ -260,7 +261,7 @@ extern "C" int rtw_render_accum_rows(rtw_ctx* c, int Nx, int Ny, int row_first, 
         const double scale = (double)iterations / (double)sampled;   // extrapolate to all iterations of all waves
         st.logic_ms = a * scale; st.traverse_ms = b * scale; st.shade_ms = d * scale; st.shadow_ms = e * scale;
     }
-    return RTW_OK;
+    return check_overflow(c, &st.stack_overflows);
 }
 
 extern "C" int rtw_tonemap(rtw_ctx* c, int Nx, int Ny, int spp_total, const float* accum_dev, float* rgba_out_dev) {

@@ -70,6 +70,7 @@ struct DScene {
     int has_media;              // scene contains constant media (ray seed needed in traversal)
     int has_motion;             // scene contains moving spheres (gather time needed by shadow rays)
     int has_images;             // scene contains image textures (sphere uv needed)
+    uint32_t* overflow;         // one device word: traversal-stack pushes that found the stack full (must stay 0)
     // shading tables
     const float4* mats;         // 1 float4 per material: (type, texture, param, -) as bit patterns
     const float4* texs;         // 2 float4 per texture: (type, r, g, b) (odd, even, scale, table/image index)
@@ -179,7 +180,8 @@ struct SmallScene {
 #define RTW_C_NEW        28
 #define RTW_C_TRACED     29
 #define RTW_C_TICKET     30                // CTAs of k_regen that have finished (the last one retires the iteration's counters)
-#define RTW_C_WORDS      32
+#define RTW_C_UNOCC_LO   32                // uint64 NEE contributions added (unoccluded shadow rays)
+#define RTW_C_WORDS      36
 
 // Per-slot state is read and written through queue indices (a warp of the shading kernels holds
 // 32 arbitrary slots), so the records that are always used together are laid out as ONE 32-byte

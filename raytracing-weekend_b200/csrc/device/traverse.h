@@ -21,6 +21,23 @@ struct TravStats {
     uint32_t prims;
 };
 
+// A push that finds the stack full is COUNTED (DScene::overflow) and dropped; the host reads the word after every
+// render / trace call and fails the call (RTW_ERR_STATE) if it is not zero — a wrong image is never returned silently.
+// With 63-bit Morton keys and index tie-breaks below 2^25 primitives a Karras hierarchy is at most 63 + 25 = 88
+// levels deep, so RTW_STACK = 96 cannot overflow on a hierarchy this library built (tests/test_gpu_edges.py builds
+// 4096 coincident primitives to show it).
+RTW_HD void push_ref(const DScene& sc, uint32_t* stack, int& sp, uint32_t ref) {
+    if (sp < RTW_STACK) {
+        stack[sp++] = ref;
+    } else if (sc.overflow) {
+#if defined(__CUDA_ARCH__)
+        atomicAdd(sc.overflow, 1u);
+#else
+        (*sc.overflow)++;
+#endif
+    }
+}
+
 template <class Mem>
 RTW_HD void fetch_node(const DScene& sc, const float4* top, uint32_t ref, float4& n0, float4& n1, float4& n2, float4& n3) {
     if (ref & RTW_REF_TOP) {
@@ -98,7 +115,7 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
             const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
             if (hl && hr) {
                 const bool left_first = tl <= tr;
-                if (sp < RTW_STACK) stack[sp++] = left_first ? cr : cl;
+                push_ref(sc, stack, sp, left_first ? cr : cl);
                 cur = left_first ? cl : cr;
             } else if (hl) {
                 cur = cl;
@@ -153,7 +170,7 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
             const bool hr = slab_test(sr, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.tmin, r.tmax, tr);
             const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
             if (hl && hr) {
-                if (sp < RTW_STACK) stack[sp++] = cr;
+                push_ref(sc, stack, sp, cr);
                 cur = cl;
             } else if (hl) {
                 cur = cl;
@@ -357,7 +374,7 @@ struct Walker {
         const uint32_t cl = f2u(n3.x), cr = f2u(n3.y);
         if (hl && hr) {
             const bool left_first = kAny || tl <= tr;
-            if (sp < RTW_STACK) stack[sp++] = left_first ? cr : cl;
+            push_ref(sc, stack, sp, left_first ? cr : cl);
             cur = left_first ? cl : cr;
         } else if (hl) {
             cur = cl;

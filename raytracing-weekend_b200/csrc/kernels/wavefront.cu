@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(kBlock) k_traverse_small(const DScene sc, cons
 __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const DWave w, const __grid_constant__ SmallScene ss) {
     const uint32_t n = w.counters[RTW_C_SHADOW];
     const uint32_t tiles = (n + kBlock - 1) / kBlock;
+    uint32_t n_unocc = 0;
     for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const uint32_t i = tile * kBlock + threadIdx.x;
         RayW r;
@@ -361,7 +362,9 @@ __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const 
         if (valid) shadow_ray_of(sc, w, i, r, c, slot);
         const bool occluded = small_any(ss, r) || !valid;
         if (valid) shadow_result(w, slot, c, occluded);
+        n_unocc += (uint32_t)__popc(__ballot_sync(0xffffffffu, valid && !occluded));
     }
+    if ((threadIdx.x & 31u) == 0u && n_unocc) atomic_add_u64(w.counters + RTW_C_UNOCC_LO, (unsigned long long)n_unocc);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
 }
 
@@ -404,12 +407,22 @@ __device__ __forceinline__ void shade_chunk(const DScene& sc, const DWave& w, ui
             r.seed = sh.seed;
         }
         const bool occluded = small_any(*ss, r);
-        if (sh.emit && !occluded) {
+        const bool add = sh.emit && !occluded;
+        if (add) {
             float4 ra = w.rad[slot];
             ra.x += sh.contrib.x; ra.y += sh.contrib.y; ra.z += sh.contrib.z;
             w.rad[slot] = ra;
         }
-        n_shadow += (uint32_t)__popc(m_shadow);   // every lane keeps the warp's count; lane 0 publishes it
+        // every lane keeps the warp's counts (NEE rays in the low half, contributions added in the high half);
+        // lane 0 publishes them once per kernel
+        n_shadow += (uint32_t)__popc(m_shadow) + ((uint32_t)__popc(__ballot_sync(0xffffffffu, add)) << 16);
+        if ((n_shadow & 0xffffu) >= 0x8000u) {   // keep the two 16-bit halves from running into each other
+            if (lane == 0) {
+                atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)(n_shadow & 0xffffu));
+                atomic_add_u64(w.counters + RTW_C_UNOCC_LO, (unsigned long long)(n_shadow >> 16));
+            }
+            n_shadow = 0u;
+        }
         m_shadow = 0u;
     }
     if ((m_regen | m_shadow | m_trace) == 0u) return;
@@ -485,7 +498,10 @@ __device__ __forceinline__ void shade_all_body(const DScene& sc, const DWave& w,
         slot = ahead;
         ahead = ahead2;
     }
-    if (kFuse && (threadIdx.x & 31u) == 0u && n_shadow) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n_shadow);
+    if (kFuse && (threadIdx.x & 31u) == 0u && n_shadow) {
+        atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)(n_shadow & 0xffffu));
+        atomic_add_u64(w.counters + RTW_C_UNOCC_LO, (unsigned long long)(n_shadow >> 16));
+    }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // ray statistics of this iteration: every queued slot was one closest-hit ray (the shadow
         // rays are counted by k_shadow, once the shadow queue is complete)

@@ -180,3 +180,33 @@ def test_upload_refuses_what_the_scene_file_loader_refuses(director, rtw):
     assert L.rtw_render(director._c, 70000, 70000, 1, 1, out.ctypes.data) == rtw.RTW_ERR_INVALID
     director.init(32, 32, 1)
     director.createScene(0)
+
+
+def test_coincident_primitives_do_not_overflow_the_traversal_stack(director, rtw, orc):
+    """4096 primitives with the SAME centroid (identical Morton keys: the Karras hierarchy is split on index bits
+    only, the deepest tree this builder can make).  The stack-overflow counter stays 0 (a dropped push would fail
+    the call with RTW_ERR_STATE) and the hits are the brute-force oracle's."""
+    import ctypes as C
+    import rayset
+    import scene_kit
+    k = scene_kit.KitScene(rtw)
+    m = k.mat(rtw.MAT_LAMBERTIAN, k.constant(0.5, 0.5, 0.5))
+    for i in range(4096):
+        k.prim(rtw.PRIM_SPHERE, [1.0, 2.0, 3.0, 0.5 + 0.0001 * (i % 7)], m)
+    k.sky = 1
+    k.cam = scene_kit.camera(rtw, (1, 2, 8), (1, 2, 3), 30, 1.5)
+    k.finish()
+    director.init(48, 32, 1)
+    director.set_option("leaf_size", 1)
+    try:
+        director.scene = k
+        director.upload(k.desc)
+        o = orc.OracleScene(k.desc, k.n_prims)
+        cam = o.camera_rays(48, 32, 0)
+        hits = director.trace_closest(cam)
+        ref, _ = o.trace_closest(cam, 0)
+        assert np.array_equal(hits["prim"], ref["prim"]) and (ref["prim"] >= 0).any()
+        director.renderFrame(1)
+        assert director.stats()["stack_overflows"] == 0
+    finally:
+        director.set_option("leaf_size", 0)
