@@ -108,6 +108,8 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "top_nodes")) {
         if (value < 0 || value > 3584) return fail(c, RTW_ERR_INVALID, "top_nodes out of range [0, 3584]");
         c->opt_top_nodes = (int)value;
+    } else if (!strcmp(name, "wide")) {
+        c->opt_wide = value ? 1 : 0;
     } else if (!strcmp(name, "leaf_size")) {
         if (value < 0 || value > RTW_MAX_LEAF_SIZE) return fail(c, RTW_ERR_INVALID, "leaf_size out of range [0, 32]");
         c->opt_leaf_size = (int)value;
@@ -368,6 +370,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
         RTW_CUDA(c, dalloc(pool, &b.leaf_mat, n));
         RTW_CUDA(c, dalloc(pool, &b.nodes, (size_t)4 * ni));
         RTW_CUDA(c, dalloc(pool, &b.top_nodes, (size_t)4 * 3584));
+        RTW_CUDA(c, dalloc(pool, &c->wide_nodes, (size_t)8 * ni));
     }
     b.max_top = c->opt_top_nodes;
     // leaf ranges: a scene of <= 16 primitives is ONE range (every lane of a warp walks the
@@ -375,6 +378,8 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // of <= 4 primitives, which trades a few extra primitive tests for fewer node visits.
     b.leaf_size = c->opt_leaf_size > 0 ? c->opt_leaf_size : (n <= 16 ? 16 : 4);
     c->leaf_size = b.leaf_size;
+    const bool wide = c->opt_wide != 0 && n > b.leaf_size;
+    b.wide = wide ? c->wide_nodes : nullptr;
     uint64_t launches = 0;
     RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
     RTW_CUDA(c, lbvh_build(c->stream, b, &launches));
@@ -400,6 +405,8 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     sc.n_leaves = n;
     sc.n_internal = ni;
     sc.n_top = (int)hb[6];
+    sc.wide = b.wide;
+    if (wide) sc.n_top = 0;   // the wide walk reads its 128-byte records through L1 (no shared-memory staging)
     if (n <= b.leaf_size) sc.root = leaf_range_ref(0, n);
     else sc.root = sc.n_top > 0 ? (RTW_REF_TOP | 0u) : 0u;
     c->n_internal = ni;

@@ -19,6 +19,7 @@ struct rtw_ctx {
     uint32_t class_mask = 0;
     std::vector<void*> scene_allocs;
     rtw::BuildBuffers build{};
+    float4* wide_nodes = nullptr;     // 8 float4 per internal node (owned by scene_allocs)
     rtw::DScene scene{};
     rtw::LaunchCfg cfg{};
     rtw::SmallScene small{};          // filled by rtw_build_accel when the scene is one leaf range of <= RTW_SMALL_MAX
@@ -56,6 +57,7 @@ struct rtw_ctx {
     // ---- options ----
     long long opt_pool_paths = 0;    // 0 = auto (rtw_render.cu)
     int opt_top_nodes = 1024;
+    int opt_wide = 1;                // LBVH scenes: walk the 4-wide nodes (lbvh.h make_wide_node); 0 = the two-child nodes
     int opt_leaf_size = 0;
     int opt_small = -1;              // -1 = auto, 0 = never, 1 = whenever the scene qualifies
     int opt_small_static = 1;        // small scenes: rects and spheres in the static table (layout.h SmallGroup)

@@ -60,6 +60,8 @@ struct DScene {
     // LBVH
     const float4* nodes;        // 4 float4 (64 B) per internal node, see lbvh.h
     const float4* top_nodes;    // n_top nodes re-indexed breadth-first for shared-memory staging
+    const float4* wide;         // 8 float4 (128 B) per internal node: the node collapsed to <= 4 children (lbvh.h make_wide_node);
+                                // nullptr = walk the two-child nodes
     const float4* prims;        // 2 float4 (32 B) per leaf
     const float2* prim_ext;     // per leaf: (time0, time1) of a moving sphere
     const int*    leaf_prim;    // leaf → index into rtw_scene_desc::prims

@@ -177,6 +177,50 @@ RTW_HD uint32_t traversal_ref(int karras_ref, int first, int last, int leaf_size
     return (uint32_t)karras_ref;
 }
 
+// ---- 4-wide nodes ---------------------------------------------------------------------------
+// Wide node i = two-child node i with every child that is itself an internal node replaced by THAT node's two
+// children: 2..4 children, one 128-byte record, half the node visits and stack traffic of the two-child walk.
+// It exists for every internal node (a child reference names the two-child node; the walk reads wide[ref]).
+//   w[0..5] = min.x min.y min.z max.x max.y max.z of children 0..3 (structure of arrays: one float4 per bound)
+//   w[6]    = the 4 child references (layout.h encoding; RTW_REF_NONE = no child, box = unreachable point)
+//   w[7]    = unused (keeps the record at 128 bytes)
+RTW_HD void node_child(const float4& n0, const float4& n1, const float4& n2, const float4& n3, int side, float3& mn, float3& mx,
+                       uint32_t& ref) {
+    if (side == 0) { mn = f3(n0.x, n0.y, n0.z); mx = f3(n0.w, n1.x, n1.y); ref = f2u(n3.x); }
+    else { mn = f3(n1.z, n1.w, n2.x); mx = f3(n2.y, n2.z, n2.w); ref = f2u(n3.y); }
+}
+RTW_HD void make_wide_node(const float4* nodes, int i, float4* w) {
+    float bx[6][4];
+    uint32_t refs[4];
+    for (int k = 0; k < 4; k++) {
+        for (int c = 0; c < 6; c++) bx[c][k] = RTW_FLT_MAX;
+        refs[k] = RTW_REF_NONE;
+    }
+    int m = 0;
+    const float4 a0 = nodes[4 * i], a1 = nodes[4 * i + 1], a2 = nodes[4 * i + 2], a3 = nodes[4 * i + 3];
+    for (int side = 0; side < 2; side++) {
+        float3 mn, mx;
+        uint32_t ref;
+        node_child(a0, a1, a2, a3, side, mn, mx, ref);
+        if (ref & RTW_REF_LEAF) {
+            bx[0][m] = mn.x; bx[1][m] = mn.y; bx[2][m] = mn.z; bx[3][m] = mx.x; bx[4][m] = mx.y; bx[5][m] = mx.z;
+            refs[m++] = ref;
+        } else {
+            const float4 b0 = nodes[4 * ref], b1 = nodes[4 * ref + 1], b2 = nodes[4 * ref + 2], b3 = nodes[4 * ref + 3];
+            for (int s2 = 0; s2 < 2; s2++) {
+                float3 cmn, cmx;
+                uint32_t cref;
+                node_child(b0, b1, b2, b3, s2, cmn, cmx, cref);
+                bx[0][m] = cmn.x; bx[1][m] = cmn.y; bx[2][m] = cmn.z; bx[3][m] = cmx.x; bx[4][m] = cmx.y; bx[5][m] = cmx.z;
+                refs[m++] = cref;
+            }
+        }
+    }
+    for (int c = 0; c < 6; c++) w[c] = make_float4(bx[c][0], bx[c][1], bx[c][2], bx[c][3]);
+    w[6] = make_float4(u2f(refs[0]), u2f(refs[1]), u2f(refs[2]), u2f(refs[3]));
+    w[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
 // Pack primitive p (material type mt) into its two-float4 leaf record.
 RTW_HD void pack_prim(const rtw_prim& p, int mattype, float4& a, float4& b, float2& ext) {
     const float meta = u2f(meta_pack(p.type, p.flip, mattype, p.type == RTW_PRIM_MOVING_SPHERE ? -1 : p.transform));

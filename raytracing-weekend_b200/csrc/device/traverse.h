@@ -14,7 +14,9 @@
 
 namespace rtw {
 
-#define RTW_STACK 96
+// deepest Karras hierarchy: 63 key bits + 25 index bits = 88 levels; the 4-wide walk visits every other level and
+// pushes at most 3 references per visit: 3 * 44 = 132
+#define RTW_STACK 136
 
 struct TravStats {
     uint32_t nodes;
@@ -24,7 +26,7 @@ struct TravStats {
 // A push that finds the stack full is COUNTED (DScene::overflow) and dropped; the host reads the word after every
 // render / trace call and fails the call (RTW_ERR_STATE) if it is not zero — a wrong image is never returned silently.
 // With 63-bit Morton keys and index tie-breaks below 2^25 primitives a Karras hierarchy is at most 63 + 25 = 88
-// levels deep, so RTW_STACK = 96 cannot overflow on a hierarchy this library built (tests/test_gpu_edges.py builds
+// levels deep, so RTW_STACK = 136 cannot overflow (see the definition) on a hierarchy this library built (tests/test_gpu_edges.py builds
 // 4096 coincident primitives to show it).
 RTW_HD void push_ref(const DScene& sc, uint32_t* stack, int& sp, uint32_t ref) {
     if (sp < RTW_STACK) {
@@ -75,6 +77,42 @@ RTW_HD bool slab_test(const SlabRay& s, float minx, float miny, float minz, floa
     return tn <= tf * 1.0000004f;
 }
 
+// ---- 4-wide nodes (lbvh.h make_wide_node): one visit = one 128-byte record, four slab tests ----
+RTW_HD void sort2(float& ta, uint32_t& ra, float& tb, uint32_t& rb) {   // ascending by t
+    const bool sw = tb < ta;
+    const float t0 = sw ? tb : ta, t1 = sw ? ta : tb;
+    const uint32_t r0 = sw ? rb : ra, r1 = sw ? ra : rb;
+    ta = t0; tb = t1; ra = r0; rb = r1;
+}
+// Visits wide node `cur`: returns the child to continue with (the nearest one for a closest-hit walk) after pushing
+// the other children the ray enters, nearest on top; RTW_REF_NONE if the ray enters none (the caller pops).
+template <class Mem, bool kAny>
+RTW_HD uint32_t visit_wide(const DScene& sc, const SlabRay& sr, uint32_t cur, float tmin, float limit, uint32_t* stack, int& sp) {
+    const float4* p = sc.wide + 8 * (size_t)cur;
+    const float4 mnx = Mem::ld4(p), mny = Mem::ld4(p + 1), mnz = Mem::ld4(p + 2);
+    const float4 mxx = Mem::ld4(p + 3), mxy = Mem::ld4(p + 4), mxz = Mem::ld4(p + 5), rf = Mem::ld4(p + 6);
+    const float kMiss = 3.0e38f;
+    float t0, t1, t2, t3;
+    const bool h0 = slab_test(sr, mnx.x, mny.x, mnz.x, mxx.x, mxy.x, mxz.x, tmin, limit, t0);
+    const bool h1 = slab_test(sr, mnx.y, mny.y, mnz.y, mxx.y, mxy.y, mxz.y, tmin, limit, t1);
+    const bool h2 = slab_test(sr, mnx.z, mny.z, mnz.z, mxx.z, mxy.z, mxz.z, tmin, limit, t2);
+    const bool h3 = slab_test(sr, mnx.w, mny.w, mnz.w, mxx.w, mxy.w, mxz.w, tmin, limit, t3);
+    uint32_t r0 = f2u(rf.x), r1 = f2u(rf.y), r2 = f2u(rf.z), r3 = f2u(rf.w);
+    // a child the ray misses (or that does not exist) sorts behind every child it enters
+    t0 = (h0 && r0 != RTW_REF_NONE) ? t0 : kMiss;
+    t1 = (h1 && r1 != RTW_REF_NONE) ? t1 : kMiss;
+    t2 = (h2 && r2 != RTW_REF_NONE) ? t2 : kMiss;
+    t3 = (h3 && r3 != RTW_REF_NONE) ? t3 : kMiss;
+    const int hits = (t0 < kMiss ? 1 : 0) + (t1 < kMiss ? 1 : 0) + (t2 < kMiss ? 1 : 0) + (t3 < kMiss ? 1 : 0);
+    if (hits == 0) return RTW_REF_NONE;
+    // (an any-hit walk needs no order, but the sort also compacts the entered children to the front)
+    sort2(t0, r0, t1, r1); sort2(t2, r2, t3, r3); sort2(t0, r0, t2, r2); sort2(t1, r1, t3, r3); sort2(t1, r1, t2, r2);
+    if (hits > 3) push_ref(sc, stack, sp, r3);
+    if (hits > 2) push_ref(sc, stack, sp, r2);
+    if (hits > 1) push_ref(sc, stack, sp, r1);
+    return r0;
+}
+
 RTW_HD int leaf_prim_of(const DScene& sc, uint32_t leaf) {
 #if defined(__CUDA_ARCH__)
     return __ldg(sc.leaf_prim + leaf);
@@ -106,6 +144,15 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
     for (;;) {
         bool exhausted = false;
         while (!(cur & RTW_REF_LEAF)) {
+            if (sc.wide) {
+                if (kStats) stats->nodes++;
+                cur = visit_wide<Mem, false>(sc, sr, cur, r.tmin, tb, stack, sp);
+                if (cur == RTW_REF_NONE) {
+                    if (sp == 0) { exhausted = true; break; }
+                    cur = stack[--sp];
+                }
+                continue;
+            }
             float4 n0, n1, n2, n3;
             fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
             if (kStats) stats->nodes++;
@@ -162,6 +209,15 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
     for (;;) {
         bool exhausted = false;
         while (!(cur & RTW_REF_LEAF)) {
+            if (sc.wide) {
+                if (kStats) stats->nodes++;
+                cur = visit_wide<Mem, true>(sc, sr, cur, r.tmin, r.tmax, stack, sp);
+                if (cur == RTW_REF_NONE) {
+                    if (sp == 0) { exhausted = true; break; }
+                    cur = stack[--sp];
+                }
+                continue;
+            }
             float4 n0, n1, n2, n3;
             fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
             if (kStats) stats->nodes++;
@@ -366,6 +422,12 @@ struct Walker {
     }
 
     RTW_HD void visit_node(const DScene& sc, const float4* top, uint32_t* stack) {
+        if (sc.wide) {
+            const uint32_t next = visit_wide<Mem, kAny>(sc, sr, cur, r.tmin, tb, stack, sp);
+            if (next == RTW_REF_NONE) pop(stack);
+            else cur = next;
+            return;
+        }
         float4 n0, n1, n2, n3;
         fetch_node<Mem>(sc, top, cur, n0, n1, n2, n3);
         float tl, tr;

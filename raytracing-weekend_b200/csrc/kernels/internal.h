@@ -42,6 +42,7 @@ struct BuildBuffers {
     int* leaf_mat;                  // n
     float4* nodes;                  // 4 * n_internal
     float4* top_nodes;              // 4 * max_top
+    float4* wide;                   // 8 * n_internal: 4-wide nodes (lbvh.h make_wide_node); built when not null
     int max_top;
     int leaf_size;                  // subtrees of <= leaf_size primitives become one leaf range (1 = plain LBVH)
 };

@@ -217,6 +217,16 @@ __global__ void __launch_bounds__(kThreads) k_build_top(const float4* __restrict
     }
 }
 
+// 4-wide nodes derived from the refitted two-child nodes: one thread per internal node
+__global__ void __launch_bounds__(kThreads) k_widen(const float4* __restrict__ nodes, int n_internal, float4* __restrict__ wide) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_internal) return;
+    float4 w[8];
+    make_wide_node(nodes, i, w);
+#pragma unroll
+    for (int k = 0; k < 8; k++) wide[8 * (size_t)i + k] = w[k];
+}
+
 }  // namespace
 
 cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches) {
@@ -251,6 +261,10 @@ cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches
     k_build_top<<<1, kThreads, sizeof(int) * (max_top > 0 ? max_top : 1), s>>>(b.nodes, n_internal, max_top, b.top_index,
                                                                               b.top_nodes, b.bounds + 6);
     l += 1;
+    if (b.wide) {
+        k_widen<<<(n_internal + kThreads - 1) / kThreads, kThreads, 0, s>>>(b.nodes, n_internal, b.wide);
+        l += 1;
+    }
     if (launches) *launches += l;
     return cudaGetLastError();
 }

@@ -279,7 +279,7 @@ __device__ __forceinline__ void walk_persistent(const DScene& sc, const DWave* w
 // straight-line per-thread traversal (device/traverse.h) beats the resumable walker by ~20 %.
 __global__ void __launch_bounds__(kBlock) k_traverse_flat(const DScene sc, const DWave w) {
     extern __shared__ float4 s_top[];
-    if (!(sc.root & RTW_REF_LEAF)) stage_top(sc, s_top);
+    if (!(sc.root & RTW_REF_LEAF) && !sc.wide) stage_top(sc, s_top);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot - lane < (uint32_t)w.P; slot += stride) {
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(kBlock) k_traverse_flat(const DScene sc, const
 
 __global__ void __launch_bounds__(kBlock) k_shadow_flat(const DScene sc, const DWave w) {
     extern __shared__ float4 s_top[];
-    if (!(sc.root & RTW_REF_LEAF)) stage_top(sc, s_top);
+    if (!(sc.root & RTW_REF_LEAF) && !sc.wide) stage_top(sc, s_top);
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n = w.counters[RTW_C_SHADOW];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) shadow_thread<MemGlobal>(sc, s_top, w, i);

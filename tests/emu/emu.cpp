@@ -24,7 +24,7 @@ struct Emu {
     // LBVH
     std::vector<unsigned long long> keys;
     std::vector<int> leaf_prim, leaf_mat;
-    std::vector<float4> leaf_mn, leaf_mx, packed, nodes, top_nodes;
+    std::vector<float4> leaf_mn, leaf_mx, packed, nodes, top_nodes, wide;
     std::vector<float2> ext;
     std::vector<int> left, right;
     // tables
@@ -227,6 +227,13 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
     sc.n_leaves = n;
     sc.n_internal = ni;
     sc.n_top = (int)queue.size();
+    // max_top < 0: walk the 4-wide nodes (k_widen in loop form), as rtw_build_accel does by default
+    if (max_top < 0 && n > leaf_size) {
+        e->wide.resize((size_t)8 * ni);
+        for (int i = 0; i < ni; i++) make_wide_node(e->nodes.data(), i, e->wide.data() + (size_t)8 * i);
+        sc.wide = e->wide.data();
+        sc.n_top = 0;
+    }
     if (n <= leaf_size) sc.root = leaf_range_ref(0, n);
     else sc.root = sc.n_top > 0 ? RTW_REF_TOP : 0u;
     return e;
