@@ -22,9 +22,24 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-NX, NY, SPP, DEPTH, SCENE = 600, 600, 1024, 20, 0
-WORKLOAD = "C2: Book-3 Cornell box (glass sphere + aluminium box), 600x600, 1024 spp, depth 20"
-METRIC = "Mpaths/s (camera samples completed per second, Cornell 600x600 1024spp)"
+# BASELINE.json's configurations as first-class bench lines (--config); C2 is the one `metric` is quoted on.
+CONFIGS = {
+    "C2": dict(scene=0, nx=600, ny=600, spp=1024,
+               workload="C2: Book-3 Cornell box (glass sphere + aluminium box), 600x600, 1024 spp, depth 20",
+               metric="Mpaths/s (camera samples completed per second, Cornell 600x600 1024spp)"),
+    "C3": dict(scene=1, nx=1920, ny=1080, spp=500,
+               workload="C3: Book-1 final random-spheres scene (528 primitives), 1920x1080, 500 spp, depth 20",
+               metric="Mpaths/s (camera samples completed per second, Book-1 final 1920x1080 500spp)"),
+    "C4": dict(scene=4, nx=800, ny=800, spp=10000,
+               workload="C4: Book-2 final scene (3410 primitives: box grid, fog, Perlin, image texture), 800x800, 10000 spp, depth 20",
+               metric="Mpaths/s (camera samples completed per second, Book-2 final 800x800 10000spp)"),
+    "C5": dict(scene=5, nx=3840, ny=2160, spp=4096,
+               workload="C5: stress scene (2^20 instanced spheres / quads, 1024 transforms), 3840x2160, 4096 spp, depth 20",
+               metric="Mpaths/s (camera samples completed per second, stress scene 3840x2160 4096spp)"),
+}
+DEPTH = 20
+NX, NY, SPP, SCENE = CONFIGS["C2"]["nx"], CONFIGS["C2"]["ny"], CONFIGS["C2"]["spp"], CONFIGS["C2"]["scene"]
+WORKLOAD, METRIC = CONFIGS["C2"]["workload"], CONFIGS["C2"]["metric"]
 
 
 def host_cores():
@@ -121,10 +136,52 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+STRESS_PRIMS = 0
+
+
 def oracle_scene(rtw):
     from oracle import oracle_py as orc
-    s = rtw.Scene(SCENE, NX, NY)
+    s = rtw.Scene(SCENE, NX, NY, n_stress_prims=STRESS_PRIMS)
     return s, orc.OracleScene(s.desc, s.desc.contents.n_prims)
+
+
+def reference_available():
+    """oracle/_ref/libref.so = the reference's own programs compiled for the host (oracle/Makefile `ref`).  Scenes 2 and 4
+    read assets/earthmap.jpg from /root/reference, which the GPU box does not have."""
+    try:
+        from oracle import ref_py
+    except Exception:
+        return None
+    if not ref_py.available(False):
+        return None
+    if SCENE in (2, 4) and not ref_py.assets_available():
+        return None
+    if SCENE > 4:
+        return None
+    return ref_py
+
+
+def reference_sample(budget_s, launches=None):
+    """Time THE REFERENCE ITSELF (kind "reference") on all host threads: Director::init + createScene once, then
+    renderFrame() repeatedly.  One launch = the reference's one and only frame, 1 spp of the workload's image
+    (raygen/raygen.cu:129 seeds sample 0; its -ns flag is stored and never used), so `launches` launches
+    trace launches x Nx x Ny paths of the same statistics as the workload's samples."""
+    ref_py = reference_available()
+    cores = host_cores()
+    s = ref_py.Session(SCENE, NX, NY, dm=False, threads=cores)
+    t0 = time.perf_counter()
+    s.launch(1)
+    t1 = time.perf_counter() - t0
+    n = launches if launches else int(max(1, min(256, budget_s / max(t1, 1e-3))))
+    t0 = time.perf_counter()
+    rays = s.launch(n)
+    dt = time.perf_counter() - t0
+    paths = float(NX) * NY * n
+    return {"value": paths / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "reference",
+            "sample": "%d launches of the reference's own programs (oracle/_ref/libref.so: its main.cpp / Director.cpp / device .cu "
+                      "files compiled for the host on the OptiX stand-in of oracle/ref_shim, glibc libm), each the %dx%d frame at 1 spp, "
+                      "depth %d, instance loop over the scene's primitives, %.1f s" % (n, NX, NY, DEPTH, dt),
+            "mrays_per_s": rays / dt / 1e6}, dt, n
 
 
 def cpu_sample(rtw, budget_s):
@@ -132,47 +189,72 @@ def cpu_sample(rtw, budget_s):
     passes of `spp` samples, sized from a 1 spp calibration pass to take about budget_s."""
     s, o = oracle_scene(rtw)
     cores = host_cores()
+    mode = 0 if s.desc.contents.n_prims <= 64 else 1
     t0 = time.perf_counter()
-    _, c = o.render(NX, NY, 1, DEPTH, n_threads=cores, mode=0)
+    _, c = o.render(NX, NY, 1, DEPTH, n_threads=cores, mode=mode)
     t1 = time.perf_counter() - t0
     spp = int(max(1, min(64, budget_s / max(t1, 1e-3))))
     t0 = time.perf_counter()
-    _, c = o.render(NX, NY, spp, DEPTH, n_threads=cores, mode=0, sample_first=1)
+    _, c = o.render(NX, NY, spp, DEPTH, n_threads=cores, mode=mode, sample_first=1)
     dt = time.perf_counter() - t0
     s.close()
     return {"value": c["paths"] / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
-            "sample": "%dx%d, %d spp (samples 1..%d of the 1024), depth %d, brute-force closest hit over 13 primitives, %.1f s"
-                      % (NX, NY, spp, spp, DEPTH, dt),
+            "sample": "%dx%d, %d spp (samples 1..%d of the %d), depth %d, %s, %.1f s"
+                      % (NX, NY, spp, spp, SPP, DEPTH, "brute-force closest hit" if mode == 0 else "host-mirror LBVH", dt),
             "mrays_per_s": (c["rays_closest"] + c["rays_shadow"]) / dt / 1e6}, dt, c
 
 
 def run_reference(args):
-    """--impl reference: the reference's OptiX build cannot be compiled here (no OptiX SDK,
-    SURVEY.md §8c), so this arm times the CPU oracle — the restatement of the reference's
-    own algorithm — on all host threads, same config, bounded sample per step."""
+    """--impl reference: the reference's own CPU-runnable implementation of the path on the box's host cores.  The OptiX
+    build needs the OptiX SDK and an RTX driver (unavailable here), but the reference's SOURCES compile for the host against
+    the stand-in of oracle/ref_shim: oracle/_ref/libref.so is its own main.cpp / Director.cpp / scene headers / 26 device .cu
+    files (kind "reference").  Where that library or its assets are missing the CPU oracle (kind "port") is timed instead.
+    The scene is built by the reference's own host code: librtw.so is not loaded by this arm."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    rtw = importlib.import_module("raytracing-weekend_b200")
-    s, o = oracle_scene(rtw)
     cores = host_cores()
-    spp = 32          # 11.5 M paths per step: about a second on 16 host threads
-    for _ in range(args.warmup):
-        o.render(NX, NY, 1, DEPTH, n_threads=cores, mode=0)
-    paths = 0
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        _, c = o.render(NX, NY, spp, DEPTH, n_threads=cores, mode=0, sample_first=spp * i)
-        paths += c["paths"]
-    dt = time.perf_counter() - t0
+    if reference_available() is not None:
+        launches = 32          # 32 x 360 000 paths per step on C2: about a second on 16 host threads
+        ref_py = reference_available()
+        sess = ref_py.Session(SCENE, NX, NY, dm=False, threads=cores)
+        for _ in range(args.warmup):
+            sess.launch(1)
+        t0 = time.perf_counter()
+        rays = 0
+        for _ in range(args.steps):
+            rays += sess.launch(launches)
+        dt = time.perf_counter() - t0
+        paths = float(NX) * NY * launches * args.steps
+        kind = "reference"
+        sample = ("%d steps x %d launches of the reference's own renderFrame() (oracle/_ref/libref.so), each the %dx%d frame at 1 spp "
+                  "(the reference traces one sample per launch whatever -ns says)" % (args.steps, launches, NX, NY))
+        note = "each step = a bounded sample: %d launches x 1 spp of the %d spp workload (%d-spp-equivalent path count)" % (launches, SPP, launches)
+    else:
+        rtw = importlib.import_module("raytracing-weekend_b200")
+        s, o = oracle_scene(rtw)
+        spp = 32
+        mode = 0 if s.desc.contents.n_prims <= 64 else 1
+        for _ in range(args.warmup):
+            o.render(NX, NY, 1, DEPTH, n_threads=cores, mode=mode)
+        paths = 0
+        rays = 0
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            _, c = o.render(NX, NY, spp, DEPTH, n_threads=cores, mode=mode, sample_first=spp * i)
+            paths += c["paths"]
+            rays += c["rays_closest"] + c["rays_shadow"]
+        dt = time.perf_counter() - t0
+        kind = "port"
+        sample = "%d steps x (%dx%d, %d spp) of the CPU oracle" % (args.steps, NX, NY, spp)
+        note = "each step = a bounded sample: %d spp of the %d spp workload (CPU oracle: oracle/_ref/libref.so or its assets are missing here)" % (spp, SPP)
     v = paths / dt / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "CPU oracle (port of the reference algorithm); each step = a bounded "
-                       "sample of %d spp of the 1024" % spp},
-            "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": cores, "kind": "port",
-                             "sample": "%d steps x (%dx%d, %d spp)" % (args.steps, NX, NY, spp)},
+            "config": {"workload": WORKLOAD, "note": note},
+            "mrays_per_s": rays / dt / 1e6,
+            "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -180,25 +262,33 @@ def run_reference(args):
 
 
 def main():
-    global NX, NY, SCENE, WORKLOAD
+    global NX, NY, SCENE, SPP, WORKLOAD, METRIC, STRESS_PRIMS
     ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS), help="BASELINE.json configuration (C2 = the one `metric` is quoted on)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--spp", type=int, default=SPP, help="override for quick checks (not the benchmark config)")
+    ap.add_argument("--spp", type=int, default=0, help="override for quick checks (not the benchmark config)")
     ap.add_argument("--pool", type=int, default=0, help="wavefront pool size override")
-    ap.add_argument("--scene", type=int, default=SCENE, help="override for profiling other configs (not the benchmark config)")
-    ap.add_argument("--nx", type=int, default=NX)
-    ap.add_argument("--ny", type=int, default=NY)
+    ap.add_argument("--scene", type=int, default=-1, help="override for profiling (not a benchmark config)")
+    ap.add_argument("--nx", type=int, default=0)
+    ap.add_argument("--ny", type=int, default=0)
+    ap.add_argument("--stress-prims", type=int, default=0, help="C5 / scene 5: primitive count (0 = 2^20)")
     ap.add_argument("--leaf-size", type=int, default=0)
     ap.add_argument("--opt", action="append", default=[], help="name=value passed to rtw_set_option (tuning runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-relmse", action="store_true", help="skip the tier-2 relMSE measurement (N=1 only; ~10 s of GPU time)")
     args = ap.parse_args()
-    if (args.scene, args.nx, args.ny) != (SCENE, NX, NY):
-        SCENE, NX, NY = args.scene, args.nx, args.ny
-        WORKLOAD = "OVERRIDE (not the benchmark config): scene %d, %dx%d, 1024 spp, depth 20" % (SCENE, NX, NY)
+    cfgd = CONFIGS[args.config]
+    SCENE, NX, NY, SPP, WORKLOAD, METRIC = cfgd["scene"], cfgd["nx"], cfgd["ny"], cfgd["spp"], cfgd["workload"], cfgd["metric"]
+    if args.scene >= 0 or args.nx or args.ny:
+        SCENE = args.scene if args.scene >= 0 else SCENE
+        NX, NY = args.nx or NX, args.ny or NY
+        WORKLOAD = "OVERRIDE (not a benchmark config): scene %d, %dx%d, %d spp, depth 20" % (SCENE, NX, NY, args.spp or SPP)
+    if not args.spp:
+        args.spp = SPP
+    STRESS_PRIMS = args.stress_prims
     if args.impl == "reference":
         return run_reference(args)
 
@@ -236,7 +326,7 @@ def main():
     for kv in args.opt:             # build-time options (walker, leaf_size, top_nodes) must precede createScene
         k, v = kv.split("=")
         d.set_option(k, int(v))
-    d.createScene(SCENE)
+    d.createScene(SCENE, n_stress_prims=args.stress_prims)
     if args.pool:
         d.set_option("pool_paths", args.pool)
     d.set_option("profile", 1)
@@ -255,7 +345,7 @@ def main():
     launches = {"n": 0}
     trace = {}      # host-side wall time of the phases of a frame on this rank (rank 0's goes into the line)
     agg = {"trav_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "logic_ms": 0.0, "render_ms": 0.0, "rays": 0, "shrays": 0, "iters": 0,
-           "waves": 1, "pool": 0}
+           "waves": 1, "pool": 0, "unocc": 0, "build_ms": 0.0}
 
     def sync_all():
         if world > 1:
@@ -289,6 +379,7 @@ def main():
             agg["logic_ms"] += st["logic_ms"]; agg["render_ms"] += st["render_ms"]
             agg["rays"] += st["rays_closest"]; agg["shrays"] += st["rays_shadow"]; agg["iters"] += st["iterations"]
             agg["waves"] = st["waves"]; agg["pool"] = st["pool_paths"]
+            agg["unocc"] += st.get("nee_unoccluded", 0); agg["build_ms"] = st["build_ms"]
 
     def frame_e2e():
         """Same frame through the public API from HOST buffers: scene upload + LBVH build +
@@ -354,34 +445,36 @@ def main():
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
                 "e2e": {"value": e2e, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": NX * NY * 16},
                 "gpu_launches": int(tot[2].item()), "clocks": clk.summary()}
-        # ---- roofline of the dominant kernel: k_traverse (closest-hit traversal) ----
-        # HBM-visible ALGORITHMIC bytes per ray: the 32-byte ray record read,
-        # hit 8 + queue entry 4 written = 44 B.  The BVH nodes / primitive records of SURVEY.md §8d
-        # (64 B x nodes + 32 B x primitives, +48 B per transformed run) are served by L1 / shared memory
-        # for this scene; they are reported beside it from the ORACLE's visit counters on its mirror
-        # of the hierarchy, not from the GPU.
-        s2, o2 = oracle_scene(rtw)
-        _, c = o2.render(NX, NY, 1, DEPTH, n_threads=host_cores(), mode=1)
-        s2.close()
-        rc = max(c["rays_closest"], 1)
-        onchip_per_ray = (64.0 * c["nodes_closest"] + 32.0 * (c["prims_closest"] - c["prims_xf_closest"]) +
-                          80.0 * c["prims_xf_closest"]) / rc
-        hbm_per_ray = 44.0
-        iters = max(agg["iters"], 1)
-        trav_s = agg["trav_ms"] * 1e-3
-        tp = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from the committed ncu capture
-        traffic_tab = json.load(open(tp)).get("dram_bytes_per_launch", {}) if os.path.exists(tp) else {}
-        # per-stage picture of one wavefront iteration (HBM-visible algorithmic bytes per unit)
+        # ---- roofline: algorithmic bytes per unit x units / live kernel time ----
+        # HBM-visible ALGORITHMIC bytes: closest-hit ray = the 32-byte ray record read + hit 8 + queue
+        # entry 4 written = 44 B; shaded vertex = queue entry 4 + slot record 64 + hit 8 read, then 64 written by a path
+        # that continues or radiance record (16 R + 16 W) + regen entry 4 by one that ends, + 48 per NEE ray emitted;
+        # shadow ray = 48 read + 32 per contribution added; finished path = 116.  Streaming wavefront (LBVH scenes
+        # without NEE): a vertex = one 80-byte entry read + one written.  The BVH nodes / primitive records of §8d
+        # (64 B x nodes + 32 B x primitives, 80 B with a transform) come from L1 / L2: they are counted by the ORACLE on
+        # its mirror of the hierarchy (a bounded 1 spp pass at reduced size), not by the GPU, and set against the measured
+        # L2 read peak (profiles/l2_peak.json) in `l2`.
+        streaming = agg["trav_ms"] == 0.0 and agg["shade_ms"] > 0.0
         n_paths = float(NX * NY * spp) * args.steps / world
+        rays_c, rays_s = max(agg["rays"], 1), agg["shrays"]
+        iters = max(agg["iters"], 1)
+        fin = n_paths / rays_c          # share of shaded vertices that end their path
+        unocc = (agg["unocc"] / rays_s) if (rays_s and agg["unocc"]) else 0.5
         stages = {}
-        fin = n_paths / max(agg["rays"], 1)          # share of shaded vertices that end their path
-        # k_shade_all per vertex: queue entry 4 + ray 32 + path 32 + hit 8 read; a continuing path writes ray 32 +
-        # path 32, an ending one its radiance record (16 R + 16 W) and a regen entry 4; + 48 per NEE ray emitted
-        shade_bpu = 76.0 + 64.0 * (1.0 - fin) + 36.0 * fin + 48.0 * agg["shrays"] / max(agg["rays"], 1)
-        for name, ms, units, bpu in (("k_traverse", agg["trav_ms"], agg["rays"], hbm_per_ray),
-                                     ("k_shade*", agg["shade_ms"], agg["rays"], shade_bpu),
-                                     ("k_shadow", agg["shadow_ms"], agg["shrays"], 72.0),
-                                     ("k_regen", agg["logic_ms"], n_paths, 116.0)):
+        if streaming:
+            table = (("k_stream_fill", agg["logic_ms"], n_paths, 80.0),
+                     ("k_stream_shade", agg["shade_ms"], rays_c, 160.0),
+                     ("k_stream_advance", agg["shadow_ms"], iters, 128.0))
+        else:
+            shade_bpu = 76.0 + 64.0 * (1.0 - fin) + 36.0 * fin + 48.0 * rays_s / rays_c
+            table = (("k_traverse", agg["trav_ms"], rays_c, 44.0),
+                     ("k_shade*", agg["shade_ms"], rays_c, shade_bpu),
+                     ("k_shadow", agg["shadow_ms"], rays_s, 48.0 + 32.0 * unocc),
+                     ("k_regen", agg["logic_ms"], n_paths, 116.0))
+        tp = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from the committed ncu capture
+        traffic_doc = json.load(open(tp)) if os.path.exists(tp) else {}
+        traffic_tab = traffic_doc.get("dram_bytes_per_launch", {}) if SCENE == 0 else {}
+        for name, ms, units, bpu in table:
             gbs = units * bpu / max(ms * 1e-3, 1e-9) / 1e9
             stages[name] = {"ms_per_iteration": ms / iters, "units_per_iteration": units / iters, "bytes_per_unit": bpu,
                             "gbs": gbs, "frac": gbs / peak, "kernel_ms_over_render_ms": ms / max(agg["render_ms"], 1e-9)}
@@ -389,45 +482,83 @@ def main():
         for name in stages:
             stages[name]["traffic"] = traffic_tab.get(name)
             stages[name]["share_of_kernel_time"] = stages[name]["ms_per_iteration"] / max(ksum, 1e-12)
-        # the dominant kernel is the stage with the largest share of the kernel time
         dom = max(stages, key=lambda k: stages[k]["ms_per_iteration"])
         ds = stages[dom]
-        # the whole step against the same roof: algorithmic HBM bytes of every stage / device time of the frames
         step_bytes = sum(v["units_per_iteration"] * v["bytes_per_unit"] for v in stages.values()) * iters
         step_gbs = step_bytes / max(agg["render_ms"] * 1e-3, 1e-9) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ds["gbs"], "peak": peak, "unit": "GB/s",
-                            "frac": ds["frac"], "traffic": ds["traffic"], "peak_source": peak_src,
-                            "bytes_per_unit": ds["bytes_per_unit"], "units_per_launch": ds["units_per_iteration"],
+                            "frac": ds["frac"], "traffic": ds["traffic"], "traffic_source": traffic_doc.get("source"),
+                            "peak_source": peak_src, "bytes_per_unit": ds["bytes_per_unit"], "units_per_launch": ds["units_per_iteration"],
                             "avg_launch_ms": ds["ms_per_iteration"],
                             "step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_frame": step_bytes / max(args.steps, 1),
                                      "note": "all stages' algorithmic HBM bytes / device time of the timed frames"},
-                            "traversal_on_chip_bytes_per_ray_survey_8d": onchip_per_ray + 96.0,
-                            "traversal_on_chip_gbs": agg["rays"] * onchip_per_ray / max(trav_s, 1e-9) / 1e9,
-                            "note": "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured "
-                                    "live with CUDA events on wave 0's stream inside the timed frames; with %d waves a launch shares the "
-                                    "device with the other waves' launches, so per-launch figures understate what the GPU moves: "
-                                    "`step` is the whole frame against the same roof, `alone` the same kernels timed with one wave. "
-                                    "traffic = dram bytes of one launch from the committed ncu capture. k_shade* gathers 64-byte slot "
-                                    "records through queue indices; the traversal kernels are instruction-issue bound: a "
-                                    "13-primitive scene is one leaf range passed by value, so their HBM share is only the state "
-                                    "stream" % waves,
+                            "note": "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured live with CUDA "
+                                    "events on wave 0's stream inside the timed frames; with %d waves a launch shares the device with the other "
+                                    "waves' launches, so per-launch figures understate what the GPU moves: `step` is the whole frame against the "
+                                    "same roof, `alone` the same kernel timed with one wave.  traffic = dram bytes of one launch from the committed "
+                                    "ncu capture (traffic_source), C2 only" % waves,
                             "stages": stages}
+        # ---- the on-chip (L1 / L2) stream of the traversal, from the ORACLE's visit counters ----
+        try:
+            s2, o2 = oracle_scene(rtw)
+            big = s2.desc.contents.n_prims > 100000
+            sx, sy = (max(NX // 8, 32), max(NY // 8, 32)) if big else (max(NX // 2, 32), max(NY // 2, 32))
+            _, c = o2.render(sx, sy, 1, DEPTH, n_threads=host_cores(), mode=1)
+            s2.close()
+            rc = max(c["rays_closest"], 1)
+            rs = max(c["rays_shadow"], 1)
+            per_c = (64.0 * c["nodes_closest"] + 32.0 * (c["prims_closest"] - c["prims_xf_closest"]) + 80.0 * c["prims_xf_closest"]) / rc
+            per_s = (64.0 * c["nodes_shadow"] + 32.0 * (c["prims_shadow"] - c["prims_xf_shadow"]) + 80.0 * c["prims_xf_shadow"]) / rs if c["rays_shadow"] else 0.0
+            l2p = os.path.join(ROOT, "profiles", "l2_peak.json")
+            l2_peak = float(json.load(open(l2p))["l2_read_gbs"]) if os.path.exists(l2p) else None
+            trav_ms = (agg["shade_ms"] if streaming else agg["trav_ms"] + agg["shadow_ms"])
+            on_chip = (agg["rays"] * per_c + agg["shrays"] * per_s) / max(trav_ms * 1e-3, 1e-9) / 1e9
+            line["roofline"]["l2"] = {"bytes_per_closest_ray_survey_8d": per_c + 96.0, "bytes_per_shadow_ray_survey_8d": per_s + 96.0,
+                                      "nodes_per_closest_ray": c["nodes_closest"] / rc, "prims_per_closest_ray": c["prims_closest"] / rc,
+                                      "achieved": on_chip, "peak": l2_peak, "unit": "GB/s", "frac": (on_chip / l2_peak) if l2_peak else None,
+                                      "sample": "oracle, host-mirror LBVH (two-child nodes, leaf ranges as the product's), %dx%d x 1 spp" % (sx, sy),
+                                      "note": "node + primitive bytes of SURVEY 8d per ray (oracle counters) x rays the GPU traced / live time of the "
+                                              "traversal kernels; for a scene that is one leaf range (C2) the records come from the constant bank, "
+                                              "not from L2"}
+        except Exception as ex:      # the mirror of a very large scene may not fit the time budget
+            line["roofline"]["l2"] = {"unavailable": str(ex)}
         if waves > 1:   # the same kernels timed without a concurrent wave (one untimed extra frame)
             d.set_option("waves", 1)
             for _ in range(2):      # the first frame re-allocates the pool
-                d.render_accum(accum.data_ptr(), 0, 1, max(spp // world, 1), DEPTH)
+                d.render_accum(accum.data_ptr(), 0, 1, max(min(spp // world, max(1, (1 << 29) // (NX * NY))), 1), DEPTH)
             s1 = d.stats()
             d.set_option("waves", 0)
             it1 = max(s1["iterations"], 1)
-            key = {"k_traverse": "traverse_ms", "k_shade*": "shade_ms", "k_shadow": "shadow_ms", "k_regen": "logic_ms"}[dom]
+            key = {"k_traverse": "traverse_ms", "k_shade*": "shade_ms", "k_shadow": "shadow_ms", "k_regen": "logic_ms",
+                   "k_stream_fill": "logic_ms", "k_stream_shade": "shade_ms", "k_stream_advance": "shadow_ms"}[dom]
             units1 = {"k_traverse": s1["rays_closest"], "k_shade*": s1["rays_closest"], "k_shadow": s1["rays_shadow"],
-                      "k_regen": s1["paths"]}[dom]
+                      "k_regen": s1["paths"], "k_stream_fill": s1["paths"], "k_stream_shade": s1["rays_closest"],
+                      "k_stream_advance": it1}[dom]
             g1 = units1 * ds["bytes_per_unit"] / max(s1[key] * 1e-3, 1e-9) / 1e9
             line["roofline"]["alone"] = {"waves": 1, "pool_paths": int(s1["pool_paths"]), "avg_launch_ms": s1[key] / it1,
                                          "units_per_launch": units1 / it1, "achieved": g1, "frac": g1 / peak,
                                          "frame_ms": s1["render_ms"]}
+        line["build"] = {"lbvh_build_ms": agg["build_ms"], "primitives": int(dsc.n_prims),
+                         "note": "device time of rtw_build_accel (inside every e2e step, outside `value`)"}
+        if world == 1 and not args.no_relmse:
+            # tier 2 of BASELINE.json at THIS configuration's image (raytracing-weekend_b200/tier2.py): the frame at the
+            # workload's sample count (and a ladder around it) against a converged frame of DISJOINT samples
+            tier2 = importlib.import_module("raytracing-weekend_b200.tier2")
+            budget_paths = 2.6e10 if SCENE == 0 else 6.0e9       # ~9 s on C2; bounded on the slower scenes
+            conv = int(max(1024, min(65536, budget_paths / (NX * NY))))
+            ladder = tuple(sorted({max(conv // 256, 1), max(conv // 64, 1), max(conv // 16, 1), max(conv // 4, 1)} | ({spp} if spp <= conv // 4 else set())))
+            m = tier2.measure(d, torch, NX, NY, ladder=ladder, converged_spp=conv, max_depth=DEPTH)
+            m["at_workload_spp"] = m["relmse"].get(str(spp))
+            m["target"] = "BASELINE.json: relMSE <= 1e-3 against the converged image"
+            line["relmse_vs_converged"] = m
         if world == 1 and not args.no_cpu_baseline:
-            cb, _, _ = cpu_sample(rtw, 15.0)
+            if reference_available() is not None:
+                cb, _, _ = reference_sample(12.0)
+                pb, _, _ = cpu_sample(rtw, 6.0)
+                cb["port_value"] = pb["value"]
+                cb["port_sample"] = pb["sample"]
+            else:
+                cb, _, _ = cpu_sample(rtw, 15.0)
             line["cpu_baseline"] = cb
         json_out.write(json.dumps(line) + "\n")
         json_out.flush()

@@ -34,12 +34,12 @@ static inline float2 make_float2(float x, float y) { return float2{x, y}; }
 // The reference's host code binds temporaries to non-const references (scene/ioScene.h:942:
 // ioTransform::translate(make_float3(...)) against `translate(float3&)`), which MSVC accepts
 // and ISO C++ does not.  For the HOST translation units only (main.cpp, Director.cpp) the
-// three-argument make_float3 therefore hands out an lvalue from a per-thread ring; the values
+// three-argument make_float3 therefore hands out an lvalue from a small ring; the values
 // are copied by every callee before the ring can wrap.
 static inline float3& make_float3(float x, float y, float z) {
-    static thread_local float3 ring[4096];
-    static thread_local unsigned next = 0;
-    float3& r = ring[next++ & 4095u];
+    static float3 ring[256];      // (host scene construction is single-threaded)
+    static unsigned next = 0;
+    float3& r = ring[next++ & 255u];
     r.x = x; r.y = y; r.z = z;
     return r;
 }

@@ -77,6 +77,7 @@ def test_top_staging_sizes_give_identical_hits(director, rtw, orc):
     Nx, Ny = 96, 96
     director.init(Nx, Ny, 1)
     ref = None
+    director.set_option("wide", 0)      # the shared-memory staging belongs to the two-child walk
     # staged-node count x leaf-range size (1 = plain LBVH: every internal node is reachable)
     for top, leaf in ((0, 1), (7, 1), (512, 1), (3584, 1), (0, 4), (7, 8), (3584, 4), (1024, 32), (1024, 0)):
         director.set_option("top_nodes", top)
@@ -89,6 +90,13 @@ def test_top_staging_sizes_give_identical_hits(director, rtw, orc):
             ref = hits
         assert np.array_equal(ref, hits)
     director.set_option("top_nodes", 1024)
+    # the 4-wide walk (the default) finds the same hits, for every leaf-range size
+    director.set_option("wide", 1)
+    for leaf in (1, 4, 32, 0):
+        director.set_option("leaf_size", leaf)
+        director.createScene(4)
+        assert director.bvh_info().n_top == 0
+        assert np.array_equal(ref, director.trace_closest(director.camera_rays(0)))
     director.set_option("leaf_size", 0)
 
 
