@@ -156,7 +156,9 @@ def reference_available():
         return None
     if SCENE in (2, 4) and not ref_py.assets_available():
         return None
-    if SCENE > 4:
+    if SCENE not in (0, 3):
+        # the stand-in's traversal is a loop over ALL instances (no hierarchy): representative for the 13 / 8 primitive
+        # scenes only; larger scenes are timed with the CPU oracle on its host-mirror LBVH (kind "port")
         return None
     return ref_py
 
