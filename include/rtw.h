@@ -273,6 +273,15 @@ int  rtw_get_linear(rtw_ctx* ctx, float* rgba_linear_mean_host, int n_floats);
 int  rtw_set_option(rtw_ctx* ctx, const char* name, int64_t value);
 int  rtw_get_stats(rtw_ctx* ctx, rtw_stats* out);
 
+/* ---- the step after the path: a denoise STAND-IN (replaces Director.cpp:887-949,988-1000) ----------
+ * The reference passes its frame through the OptiX AI denoiser, a closed network inside the driver that
+ * cannot be matched; this entry point is a documented, DIFFERENT filter (edge-avoiding a-trous wavelet,
+ * `iterations` passes 1..8 with tap spacing 2^i, colour weight 1 / (1 + d^2 / sigma^2)) on the same
+ * gamma-encoded float4 frame, excluded from parity with the reference and never applied by rtw_render.
+ * Host buffers in and out (Nx*Ny*4 floats each, may alias). */
+int  rtw_denoise(rtw_ctx* ctx, int Nx, int Ny, int iterations, float sigma,
+                 const float* rgba_in_host, float* rgba_out_host);
+
 /* ---- several GPUs of one box (SURVEY.md §8b `rtw_create(const int* devices, int n, ...)`, §8e) ----
  * One context, one worker thread and one stream set per listed GPU; scene and LBVH are replicated.
  * rtw_multi_render shards a frame by SAMPLE (GPU g renders samples k = g (mod G); one

@@ -1325,3 +1325,42 @@ extern "C" void orc_tonemap(int n_pixels, int spp, const float* sum, float* out)
         out[i * 4 + 3] = 1.f;
     }
 }
+
+// ============================================================================
+// Denoise stand-in (the step after the path; the reference: Director.cpp:887-949,988-1000, OptiX AI denoiser —
+// a closed network, NOT restated).  This restates the product's documented replacement filter
+// (raytracing-weekend_b200/csrc/kernels/denoise.cu) so that it has a CPU checker of its own: `iterations` a-trous
+// passes, tap spacing 2^i, B3-spline taps (1,4,6,4,1)/16, colour weight 1 / (1 + d^2 / sigma^2), taps outside the
+// image skipped, sums in row-major tap order, alpha copied.  Parity with the reference is not claimed for this step.
+// ============================================================================
+extern "C" void orc_denoise(int Nx, int Ny, int iterations, float sigma, const float* in, float* out) {
+    const size_t n = (size_t)Nx * Ny;
+    std::vector<float> a(in, in + n * 4), b(n * 4);
+    const float inv_sigma2 = 1.0f / (sigma * sigma);
+    const float h[5] = {0.0625f, 0.25f, 0.375f, 0.25f, 0.0625f};
+    for (int it = 0; it < iterations; it++) {
+        const int step = 1 << it;
+        for (int y = 0; y < Ny; y++)
+            for (int x = 0; x < Nx; x++) {
+                const float* c = &a[((size_t)y * Nx + x) * 4];
+                float sr = 0.f, sg = 0.f, sb = 0.f, sw = 0.f;
+                for (int dy = -2; dy <= 2; dy++) {
+                    const int qy = y + dy * step;
+                    if (qy < 0 || qy >= Ny) continue;
+                    for (int dx = -2; dx <= 2; dx++) {
+                        const int qx = x + dx * step;
+                        if (qx < 0 || qx >= Nx) continue;
+                        const float* q = &a[((size_t)qy * Nx + qx) * 4];
+                        const float dr = q[0] - c[0], dg = q[1] - c[1], db = q[2] - c[2];
+                        const float d2 = dr * dr + dg * dg + db * db;
+                        const float w = (h[dx + 2] * h[dy + 2]) / (1.0f + d2 * inv_sigma2);
+                        sr += w * q[0]; sg += w * q[1]; sb += w * q[2]; sw += w;
+                    }
+                }
+                float* o = &b[((size_t)y * Nx + x) * 4];
+                o[0] = sr / sw; o[1] = sg / sw; o[2] = sb / sw; o[3] = c[3];
+            }
+        a.swap(b);
+    }
+    memcpy(out, a.data(), n * 4 * sizeof(float));
+}

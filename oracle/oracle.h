@@ -89,6 +89,9 @@ int  orc_bvh_download(const orc_scene* s, uint64_t* morton, int32_t* leaf_prim,
 /* per-primitive world AABBs as the builder sees them: 6 floats per prim */
 void orc_prim_aabbs(const orc_scene* s, float* aabbs);
 
+/* the product's denoise stand-in (csrc/kernels/denoise.cu), restated; NOT the reference's OptiX AI denoiser */
+void orc_denoise(int Nx, int Ny, int iterations, float sigma, const float* rgba_in, float* rgba_out);
+
 /* texture evaluation hook (tests) */
 void orc_texture_eval(const orc_scene* s, int texture, float u, float v,
                       const float* p, float* rgb_out);

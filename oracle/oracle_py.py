@@ -69,6 +69,8 @@ def lib():
     L.orc_bvh_download.argtypes = [vp, vp, vp, vp, vp, vp]
     L.orc_prim_aabbs.restype = None
     L.orc_prim_aabbs.argtypes = [vp, vp]
+    L.orc_denoise.restype = None
+    L.orc_denoise.argtypes = [i32, i32, i32, C.c_float, vp, vp]
     L.orc_texture_eval.restype = None
     L.orc_texture_eval.argtypes = [vp, i32, C.c_float, C.c_float, vp, vp]
     _lib = L
@@ -209,4 +211,12 @@ class OracleScene:
 def tonemap(sums, spp):
     out = np.empty_like(sums)
     lib().orc_tonemap(sums.shape[0] * sums.shape[1], spp, _ptr(np.ascontiguousarray(sums)), _ptr(out))
+    return out
+
+
+def denoise(frame, iterations=3, sigma=0.25):
+    """The product's denoise stand-in restated on the CPU (oracle.cpp orc_denoise)."""
+    frame = np.ascontiguousarray(frame, np.float32)
+    out = np.empty_like(frame)
+    lib().orc_denoise(frame.shape[1], frame.shape[0], iterations, sigma, _ptr(frame), _ptr(out))
     return out

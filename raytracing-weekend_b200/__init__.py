@@ -119,7 +119,7 @@ ABI_SYMBOLS = [
     "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval", "rtw_scene_save", "rtw_scene_load", "rtw_scene_io_error",
     "rtw_render_accum_rows", "rtw_create_multi", "rtw_multi_destroy", "rtw_multi_last_error", "rtw_multi_device_count",
     "rtw_multi_uses_nccl", "rtw_multi_set_option", "rtw_multi_upload_scene", "rtw_multi_build_accel", "rtw_multi_render",
-    "rtw_multi_get_linear", "rtw_multi_get_stats",
+    "rtw_multi_get_linear", "rtw_multi_get_stats", "rtw_denoise",
 ]
 
 _lib = None
@@ -170,6 +170,7 @@ def lib():
         "rtw_scene_load": (i32, [C.c_char_p, C.POINTER(vp)]),
         "rtw_scene_io_error": (C.c_char_p, []),
         "rtw_write_ppm": (i32, [C.c_char_p, i32, i32, vp]),
+        "rtw_denoise": (i32, [vp, i32, i32, i32, C.c_float, vp, vp]),
         "rtw_render_accum_rows": (i32, [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
         "rtw_create_multi": (i32, [C.POINTER(i32), i32, C.POINTER(vp)]),
         "rtw_multi_destroy": (i32, [vp]),
@@ -307,6 +308,13 @@ class Director:
                                       C.c_void_p(out_dev_ptr)), "rtw_tonemap")
 
     # Director::printPPM()
+    def denoise(self, frame, iterations=3, sigma=0.25):
+        """The denoise STAND-IN (rtw_denoise): an a-trous filter, not the reference's OptiX AI denoiser."""
+        frame = np.ascontiguousarray(frame, np.float32)
+        out = np.empty_like(frame)
+        self._check(lib().rtw_denoise(self._c, frame.shape[1], frame.shape[0], iterations, sigma, _ptr(frame), _ptr(out)), "rtw_denoise")
+        return out
+
     def printPPM(self, path="-"):
         self._check(lib().rtw_write_ppm(path.encode(), self.Nx, self.Ny, _ptr(self.frame)), "rtw_write_ppm")
 

@@ -316,3 +316,25 @@ extern "C" int rtw_get_linear(rtw_ctx* c, float* out, int n_floats) {
     }
     return RTW_OK;
 }
+
+extern "C" int rtw_denoise(rtw_ctx* c, int Nx, int Ny, int iterations, float sigma, const float* in_host, float* out_host) {
+    if (!c) return RTW_ERR_INVALID;
+    if (!in_host || !out_host || Nx <= 0 || Ny <= 0 || iterations < 1 || iterations > 8 || !(sigma > 0.f) ||
+        (unsigned long long)Nx * (unsigned long long)Ny > 0x7fffffffull)
+        return fail(c, RTW_ERR_INVALID, "bad denoise arguments");
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    const size_t bytes = sizeof(float4) * (size_t)Nx * Ny;
+    float4 *a = nullptr, *b = nullptr, *res = nullptr;
+    RTW_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&a), bytes));
+    if (cudaMalloc(reinterpret_cast<void**>(&b), bytes) != cudaSuccess) { cudaFree(a); return fail(c, RTW_ERR_CUDA, "cudaMalloc"); }
+    uint64_t l = 0;
+    cudaError_t e = cudaMemcpyAsync(a, in_host, bytes, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = launch_denoise(c->stream, Nx, Ny, iterations, sigma, a, b, &res, &l);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_host, res, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(a);
+    cudaFree(b);
+    if (e != cudaSuccess) return cuda_fail(c, e, "rtw_denoise");
+    c->stats.kernel_launches += l;
+    return RTW_OK;
+}

@@ -74,6 +74,11 @@ void Director::renderFrame() {
     check(rtw_get_stats(m_ctx, &m_stats), "rtw_get_stats");
 }
 
+void Director::denoise(int iterations, float sigma) {
+    if (!m_ctx) { std::cerr << "WARNING: -denoise needs a one-GPU context; frame left as rendered" << std::endl; return; }
+    check(rtw_denoise(m_ctx, m_Nx, m_Ny, iterations, sigma, m_frame.data(), m_frame.data()), "rtw_denoise");
+}
+
 void Director::printPPM(const char* path) {
     int rc = rtw_write_ppm(path, m_Nx, m_Ny, m_frame.data());
     if (rc != RTW_OK) {

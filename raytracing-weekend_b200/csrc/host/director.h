@@ -16,6 +16,7 @@ public:
     void createSceneFromFile(const char* path);    // scene wire format (rtw_scene_load) instead of a built-in scene function
     void saveScene(const char* path);              // rtw_scene_save of the scene in use
     void renderFrame();                                                          // Director.cpp:971
+    void denoise(int iterations, float sigma = 0.25f);   // stand-in for Director.cpp:988-1000 (a-trous filter, rtw_denoise); 1-GPU contexts
     void printPPM(const char* path = "-");                                       // Director.cpp:1010
     void destroy();                                                              // Director.cpp:86
 

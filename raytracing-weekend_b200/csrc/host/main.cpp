@@ -52,6 +52,7 @@ int main(int argc, char* argv[]) {
     -d N           CUDA device index (default 0).
     -gpus N        Render on N GPUs of this box (devices d .. d+N-1): samples or image tiles are sharded,
                    one NCCL reduce / gather per frame.
+    -denoise N     Pass the frame through N (1..8) passes of the a-trous stand-in for the reference's OptiX AI denoiser.
     -a DIR         Asset directory holding earthmap.ppm (default "assets").
     -j             Print one JSON line with render statistics on stderr.
     -f FILE        Render the scene stored in FILE (scene wire format) instead of scene -s N.
@@ -143,6 +144,9 @@ int main(int argc, char* argv[]) {
     else director.createScene(Nscene);
     if (!scene_out.empty()) director.saveScene(scene_out.c_str());
     director.renderFrame();
+    int dn = 0;
+    const std::string& dns = cl_input.getCmdOption("-denoise");
+    if (!dns.empty() && parse_int(dns, dn) && dn > 0) director.denoise(dn > 8 ? 8 : dn);
     auto stop = std::chrono::system_clock::now();
     auto time_seconds = std::chrono::duration<float>(stop - start).count();
     std::cerr << "INFO: Took " << time_seconds << " seconds." << std::endl;   // main.cpp:160 (Q35: whole run)

@@ -82,6 +82,10 @@ cudaError_t launch_tail(cudaStream_t s, const DScene& sc, const DWave& w, const 
 cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches);
 cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
 
+// ---- denoise stand-in (kernels/denoise.cu): `iterations` a-trous passes ping-ponging between a and b ----
+cudaError_t launch_denoise(cudaStream_t s, int Nx, int Ny, int iterations, float sigma, float4* a, float4* b, float4** result,
+                           uint64_t* launches);
+
 // ---- test hooks --------------------------------------------------------------
 cudaError_t launch_trace(cudaStream_t s, const DScene& sc, const LaunchCfg& cfg, const rtw_ray* rays, int n,
                          rtw_hit* hits, int32_t* occluded, uint32_t* work2 /* 2 device words */, uint64_t* launches);

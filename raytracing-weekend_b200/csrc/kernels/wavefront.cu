@@ -368,7 +368,12 @@ __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const 
     if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
 }
 
-__global__ void __launch_bounds__(kBlock) k_traverse(const DScene sc, const DWave w, const WalkCfg wc) {
+// resident CTAs per SM the persistent walkers' registers are held to: 4 -> 64 registers, 24-90 bytes of spills.
+// Measured (profiles/r02/lbvh_r02.md): scene 4 432 -> 453 Mpaths/s, C5 204 -> 210 against 3 CTAs / 76 registers.
+#ifndef RTW_WALK_CTAS
+#define RTW_WALK_CTAS 4
+#endif
+__global__ void __launch_bounds__(kBlock, RTW_WALK_CTAS) k_traverse(const DScene sc, const DWave w, const WalkCfg wc) {
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
     const ClosestJob job{sc, w};
@@ -523,7 +528,7 @@ __global__ void __launch_bounds__(kBlock, kCtas) k_shade_all_fused(const DScene 
 }
 
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const DWave w, const WalkCfg wc) {
+__global__ void __launch_bounds__(kBlock, RTW_WALK_CTAS) k_shadow(const DScene sc, const DWave w, const WalkCfg wc) {
     extern __shared__ float4 s_top[];
     stage_top(sc, s_top);
     const ShadowJob job{sc, w};
