@@ -273,6 +273,20 @@ int  rtw_get_linear(rtw_ctx* ctx, float* rgba_linear_mean_host, int n_floats);
 int  rtw_set_option(rtw_ctx* ctx, const char* name, int64_t value);
 int  rtw_get_stats(rtw_ctx* ctx, rtw_stats* out);
 
+/* ---- the step between scene description and launch, on the device ------------
+ * The reference inverts instance transforms inside optixAccelBuild and bakes its textures on the host, serially
+ * (Director.cpp:498-519 -> texture/ioTexture.h:181-216 Perlin tables, :228-266 image decode / flip / upload).
+ * These entry points do the same three steps as CUDA kernels; their outputs go straight into an rtw_scene_desc and
+ * are BIT-EQUAL to what the host scene builder (rtw_scene_create) computes.  Host buffers in and out.
+ *   rtw_bake_transforms  o2w_rows: n x 12 floats (row-major 3x4 object->world); out[i] = {o2w, w2o}
+ *   rtw_bake_perlin      tables first_table .. first_table + n_tables - 1 of the stream of std::mt19937(mt_seed)
+ *                        + uniform_real_distribution<float>(0,1) (the reference seeds 0; a table takes 1533 draws)
+ *   rtw_bake_image       pixels: h rows top-down, `channels` (3 or 4) bytes per pixel; rgba_out: w*h*4 bytes,
+ *                        row 0 = bottom row of the picture (v == 0), alpha 255 for 3-channel input */
+int  rtw_bake_transforms(rtw_ctx* ctx, const float* o2w_rows, int n, rtw_transform* out);
+int  rtw_bake_perlin(rtw_ctx* ctx, uint32_t mt_seed, int first_table, int n_tables, rtw_perlin* out);
+int  rtw_bake_image(rtw_ctx* ctx, const uint8_t* pixels, int width, int height, int channels, uint8_t* rgba_out);
+
 /* ---- the step after the path: a denoise STAND-IN (replaces Director.cpp:887-949,988-1000) ----------
  * The reference passes its frame through the OptiX AI denoiser, a closed network inside the driver that
  * cannot be matched; this entry point is a documented, DIFFERENT filter (edge-avoiding a-trous wavelet,

@@ -120,6 +120,7 @@ ABI_SYMBOLS = [
     "rtw_render_accum_rows", "rtw_create_multi", "rtw_multi_destroy", "rtw_multi_last_error", "rtw_multi_device_count",
     "rtw_multi_uses_nccl", "rtw_multi_set_option", "rtw_multi_upload_scene", "rtw_multi_build_accel", "rtw_multi_render",
     "rtw_multi_get_linear", "rtw_multi_get_stats", "rtw_denoise",
+    "rtw_bake_transforms", "rtw_bake_perlin", "rtw_bake_image",
 ]
 
 _lib = None
@@ -170,6 +171,9 @@ def lib():
         "rtw_scene_load": (i32, [C.c_char_p, C.POINTER(vp)]),
         "rtw_scene_io_error": (C.c_char_p, []),
         "rtw_write_ppm": (i32, [C.c_char_p, i32, i32, vp]),
+        "rtw_bake_transforms": (i32, [vp, vp, i32, vp]),
+        "rtw_bake_perlin": (i32, [vp, u32, i32, i32, vp]),
+        "rtw_bake_image": (i32, [vp, vp, i32, i32, i32, vp]),
         "rtw_denoise": (i32, [vp, i32, i32, i32, C.c_float, vp, vp]),
         "rtw_render_accum_rows": (i32, [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
         "rtw_create_multi": (i32, [C.POINTER(i32), i32, C.POINTER(vp)]),

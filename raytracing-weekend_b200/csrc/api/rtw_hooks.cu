@@ -170,3 +170,48 @@ extern "C" int rtw_sort_pairs(rtw_ctx* c, uint64_t* keys, uint32_t* values, int 
     RTW_CUDA(c, cudaStreamSynchronize(c->stream));
     return RTW_OK;
 }
+
+// ---- GPU-side scene flattening / texture baking (kernels/bake.cu) ----
+extern "C" int rtw_bake_transforms(rtw_ctx* c, const float* o2w_rows, int n, rtw_transform* out) {
+    if (!c || !o2w_rows || !out || n < 0) return RTW_ERR_INVALID;
+    if (n == 0) return RTW_OK;
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    Tmp t;
+    float* d_in = nullptr;
+    rtw_transform* d_out = nullptr;
+    RTW_CUDA(c, dalloc(t.pool, &d_in, (size_t)12 * n));
+    RTW_CUDA(c, dalloc(t.pool, &d_out, n));
+    RTW_CUDA(c, cudaMemcpyAsync(d_in, o2w_rows, sizeof(float) * 12 * n, cudaMemcpyHostToDevice, c->stream));
+    RTW_CUDA(c, launch_invert_transforms(c->stream, d_in, n, d_out));
+    RTW_CUDA(c, cudaMemcpyAsync(out, d_out, sizeof(rtw_transform) * n, cudaMemcpyDeviceToHost, c->stream));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTW_OK;
+}
+extern "C" int rtw_bake_perlin(rtw_ctx* c, uint32_t mt_seed, int first_table, int n_tables, rtw_perlin* out) {
+    if (!c || !out || first_table < 0 || n_tables < 0 || n_tables > 4096) return RTW_ERR_INVALID;
+    if (n_tables == 0) return RTW_OK;
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    Tmp t;
+    float* d_draws = nullptr;
+    rtw_perlin* d_out = nullptr;
+    RTW_CUDA(c, dalloc(t.pool, &d_draws, (size_t)1533 * n_tables));
+    RTW_CUDA(c, dalloc(t.pool, &d_out, n_tables));
+    RTW_CUDA(c, launch_perlin_tables(c->stream, mt_seed, first_table, n_tables, d_draws, d_out));
+    RTW_CUDA(c, cudaMemcpyAsync(out, d_out, sizeof(rtw_perlin) * n_tables, cudaMemcpyDeviceToHost, c->stream));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTW_OK;
+}
+extern "C" int rtw_bake_image(rtw_ctx* c, const uint8_t* pixels, int w, int h, int channels, uint8_t* rgba_out) {
+    if (!c || !pixels || !rgba_out || w <= 0 || h <= 0 || (channels != 3 && channels != 4) || (long long)w * h > 0x7fffffffll) return RTW_ERR_INVALID;
+    RTW_CUDA(c, cudaSetDevice(c->device));
+    Tmp t;
+    uint8_t* d_in = nullptr;
+    uchar4* d_out = nullptr;
+    RTW_CUDA(c, dalloc(t.pool, &d_in, (size_t)w * h * channels));
+    RTW_CUDA(c, dalloc(t.pool, &d_out, (size_t)w * h));
+    RTW_CUDA(c, cudaMemcpyAsync(d_in, pixels, (size_t)w * h * channels, cudaMemcpyHostToDevice, c->stream));
+    RTW_CUDA(c, launch_flip_rgba(c->stream, d_in, w, h, channels, d_out));
+    RTW_CUDA(c, cudaMemcpyAsync(rgba_out, d_out, (size_t)w * h * 4, cudaMemcpyDeviceToHost, c->stream));
+    RTW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTW_OK;
+}

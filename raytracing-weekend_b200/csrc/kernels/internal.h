@@ -82,6 +82,11 @@ cudaError_t launch_tail(cudaStream_t s, const DScene& sc, const DWave& w, const 
 cudaError_t launch_add_count(cudaStream_t s, int n_pixels, int count, float4* accum, uint64_t* launches);
 cudaError_t launch_tonemap(cudaStream_t s, int n_pixels, int spp, const float4* accum, float4* out, uint64_t* launches);
 
+// ---- GPU-side scene flattening / texture baking (kernels/bake.cu) ----
+cudaError_t launch_invert_transforms(cudaStream_t s, const float* o2w, int n, rtw_transform* out);
+cudaError_t launch_perlin_tables(cudaStream_t s, uint32_t seed, int first_table, int n_tables, float* draws /* 1533 * n_tables */, rtw_perlin* out);
+cudaError_t launch_flip_rgba(cudaStream_t s, const uint8_t* src, int w, int h, int channels, uchar4* dst);
+
 // ---- denoise stand-in (kernels/denoise.cu): `iterations` a-trous passes ping-ponging between a and b ----
 cudaError_t launch_denoise(cudaStream_t s, int Nx, int Ny, int iterations, float sigma, float4* a, float4* b, float4** result,
                            uint64_t* launches);
