@@ -456,7 +456,7 @@ def main():
         # (64 B x nodes + 32 B x primitives, 80 B with a transform) come from L1 / L2: they are counted by the ORACLE on
         # its mirror of the hierarchy (a bounded 1 spp pass at reduced size), not by the GPU, and set against the measured
         # L2 read peak (profiles/l2_peak.json) in `l2`.
-        streaming = agg["trav_ms"] == 0.0 and agg["shade_ms"] > 0.0
+        streaming = agg["shade_ms"] > 0.0 and agg["trav_ms"] < 0.02 * agg["shade_ms"]   # (the streaming variant records two events back to back there)
         n_paths = float(NX * NY * spp) * args.steps / world
         rays_c, rays_s = max(agg["rays"], 1), agg["shrays"]
         iters = max(agg["iters"], 1)
