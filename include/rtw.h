@@ -296,6 +296,25 @@ int  rtw_bake_image(rtw_ctx* ctx, const uint8_t* pixels, int width, int height, 
 int  rtw_denoise(rtw_ctx* ctx, int Nx, int Ny, int iterations, float sigma,
                  const float* rgba_in_host, float* rgba_out_host);
 
+/* ---- the same filter without any allocation -----------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * rtw_denoise_static computes what rtw_denoise computes, bit for bit, on DEVICE buffers the caller owns
+ * (Nx*Ny float4 each, on the context's device; they must NOT overlap: the input is read-only) and keeps its
+ * ping-pong buffer in a file-scope `static __device__` array inside the library
+ * (csrc/kernels/denoise.cu: RTW_DENOISE_STATIC_MAX_PIXELS float4 = 8 MiB, held by every GPU that loads the
+ * library until the process exits).  It calls no cudaMalloc / cudaFree / allocating routine and does not
+ * synchronise: the `iterations` passes are enqueued on `cuda_stream` (a cudaStream_t; NULL = the context's
+ * own stream) and the call returns.  Nx*Ny > RTW_DENOISE_STATIC_MAX_PIXELS is refused with RTW_ERR_INVALID
+ * (rtw_last_error names the limit).  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress); make that call outside a stream capture.  All calls on one device share the
+ * array: calls that overlap on the GPU (different streams or host threads) RACE — serialise them.  The
+ * array keeps the last call's contents; nothing in it has to start at zero (every pass overwrites all
+ * Nx*Ny pixels of its destination before they are read). */
+#define RTW_DENOISE_STATIC_MAX_PIXELS (1 << 19)
+int  rtw_denoise_static(rtw_ctx* ctx, int Nx, int Ny, int iterations, float sigma,
+                        const float* rgba_in_dev, float* rgba_out_dev, void* cuda_stream);
+
 /* ---- several GPUs of one box (SURVEY.md §8b `rtw_create(const int* devices, int n, ...)`, §8e) ----
  * One context, one worker thread and one stream set per listed GPU; scene and LBVH are replicated.
  * rtw_multi_render shards a frame by SAMPLE (GPU g renders samples k = g (mod G); one

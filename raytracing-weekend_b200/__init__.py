@@ -119,9 +119,11 @@ ABI_SYMBOLS = [
     "rtw_scene_free", "rtw_write_ppm", "rtw_math_eval", "rtw_scene_save", "rtw_scene_load", "rtw_scene_io_error",
     "rtw_render_accum_rows", "rtw_create_multi", "rtw_multi_destroy", "rtw_multi_last_error", "rtw_multi_device_count",
     "rtw_multi_uses_nccl", "rtw_multi_set_option", "rtw_multi_upload_scene", "rtw_multi_build_accel", "rtw_multi_render",
-    "rtw_multi_get_linear", "rtw_multi_get_stats", "rtw_denoise",
+    "rtw_multi_get_linear", "rtw_multi_get_stats", "rtw_denoise", "rtw_denoise_static",
     "rtw_bake_transforms", "rtw_bake_perlin", "rtw_bake_image",
 ]
+
+DENOISE_STATIC_MAX_PIXELS = 1 << 19      # RTW_DENOISE_STATIC_MAX_PIXELS (include/rtw.h)
 
 _lib = None
 
@@ -175,6 +177,7 @@ def lib():
         "rtw_bake_perlin": (i32, [vp, u32, i32, i32, vp]),
         "rtw_bake_image": (i32, [vp, vp, i32, i32, i32, vp]),
         "rtw_denoise": (i32, [vp, i32, i32, i32, C.c_float, vp, vp]),
+        "rtw_denoise_static": (i32, [vp, i32, i32, i32, C.c_float, vp, vp, vp]),
         "rtw_render_accum_rows": (i32, [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
         "rtw_create_multi": (i32, [C.POINTER(i32), i32, C.POINTER(vp)]),
         "rtw_multi_destroy": (i32, [vp]),
@@ -318,6 +321,12 @@ class Director:
         out = np.empty_like(frame)
         self._check(lib().rtw_denoise(self._c, frame.shape[1], frame.shape[0], iterations, sigma, _ptr(frame), _ptr(out)), "rtw_denoise")
         return out
+
+    def denoise_static(self, in_dev_ptr, out_dev_ptr, Nx, Ny, iterations=3, sigma=0.25, cuda_stream=None):
+        """rtw_denoise_static: the same filter on caller-owned DEVICE buffers, no allocation, no synchronisation
+        (scratch = a static __device__ array in librtw.so, at most DENOISE_STATIC_MAX_PIXELS pixels)."""
+        self._check(lib().rtw_denoise_static(self._c, Nx, Ny, iterations, sigma, C.c_void_p(in_dev_ptr), C.c_void_p(out_dev_ptr),
+                                             C.c_void_p(cuda_stream or 0)), "rtw_denoise_static")
 
     def printPPM(self, path="-"):
         self._check(lib().rtw_write_ppm(path.encode(), self.Nx, self.Ny, _ptr(self.frame)), "rtw_write_ppm")
