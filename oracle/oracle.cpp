@@ -112,6 +112,7 @@ struct orc_scene {
     bool bvh_built = false;
     int leaf_size = 1;    // subtrees of <= leaf_size leaves are walked as one primitive list (DESIGN.md "LBVH")
     std::vector<uint64_t> morton;
+    int n_tree = 0;       // leaves under the hierarchy; leaves [n_tree, n) are the product's "oversize list" (csrc/device/lbvh.h)
     std::vector<int32_t> leaf_prim;
     std::vector<BvhNode> nodes;
     Aabb scene_box{};
@@ -541,21 +542,42 @@ extern "C" int orc_bvh_build(orc_scene* s) {
     }
     s->scene_box = sb;
     V3 ext = sb.mx - sb.mn;
+    // The product keeps primitives whose box is large against the spread of the box centroids out of the hierarchy
+    // (csrc/device/lbvh.h "oversize primitives"; no counterpart in the reference, whose acceleration structure is
+    // OptiX's): box extent > 1/4 of the largest extent of the centroid bounds -> key bit 63 (sorts last); when 1..8
+    // primitives are flagged and at least 2 are not, the hierarchy covers only the unflagged leaves.
+    Aabb cb;
+    cb.mn = v3(FLT_MAX);
+    cb.mx = v3(-FLT_MAX);
+    for (int i = 0; i < n; i++) {
+        V3 c = (boxes[i].mn + boxes[i].mx) * 0.5f;
+        cb.mn = vmin(cb.mn, c);
+        cb.mx = vmax(cb.mx, c);
+    }
+    const V3 cext = cb.mx - cb.mn;
+    const float spread = fmaxf(fmaxf(cext.x, cext.y), cext.z);
+    int flagged = 0;
     std::vector<std::pair<uint64_t, int>> keys(n);
     for (int i = 0; i < n; i++) {
         V3 c = (boxes[i].mn + boxes[i].mx) * 0.5f;
-        keys[i] = {morton63(c, sb.mn, ext), i};
+        uint64_t key = morton63(c, sb.mn, ext);
+        const V3 be = boxes[i].mx - boxes[i].mn;
+        if (fmaxf(fmaxf(be.x, be.y), be.z) > 0.25f * spread) { key |= 1ull << 63; flagged++; }
+        keys[i] = {key, i};
     }
+    const int n_all = n;
+    const int m = (flagged > 0 && flagged <= 8 && n_all - flagged >= 2) ? n_all - flagged : n_all;
+    s->n_tree = m;
     std::stable_sort(keys.begin(), keys.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
     s->morton.resize(n);
     s->leaf_prim.resize(n);
     for (int i = 0; i < n; i++) { s->morton[i] = keys[i].first; s->leaf_prim[i] = keys[i].second; }
-    const int ni = std::max(n - 1, 1);
+    const int ni = std::max(m - 1, 1);
     s->nodes.assign(ni, BvhNode{});
     std::vector<int> leaf_parent(n, -1);
     const uint64_t* k = s->morton.data();
     auto delta = [&](int i, int j) -> int {
-        if (j < 0 || j >= n) return -1;
+        if (j < 0 || j >= m) return -1;
         if (k[i] == k[j]) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
         return clz64(k[i] ^ k[j]);
     };
@@ -569,7 +591,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
         return 0;
     }
     s->nodes[0].parent = -1;
-    for (int i = 0; i < n - 1; i++) {  // Karras 2012
+    for (int i = 0; i < m - 1; i++) {  // Karras 2012, over the leaves in front of the oversize list
         int d = (delta(i, i + 1) - delta(i, i - 1)) >= 0 ? 1 : -1;
         int dmin = delta(i, i - d);
         int lmax = 2;
@@ -596,7 +618,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
     }
     // bottom-up refit
     std::vector<int> visits(ni, 0);
-    for (int leaf = 0; leaf < n; leaf++) {
+    for (int leaf = 0; leaf < m; leaf++) {
         int cur = leaf_parent[leaf];
         while (cur >= 0) {
             if (visits[cur]++ == 0) break;  // first arrival stops, second computes
@@ -696,7 +718,8 @@ static bool trace_closest(const orc_scene& s, const Ray& r, int mode, float& t_b
     int stack[128];
     int sp = 0;
     int cur = 0;  // >= 0 internal node, < 0 leaf ~ref
-    const int n_leaves = (int)s.leaf_prim.size();
+    const int n_leaves = s.n_tree;
+    for (int j = s.n_tree; j < (int)s.leaf_prim.size(); j++) consider(s.leaf_prim[j]);   // the oversize list, as the product walks it
     // a subtree of <= leaf_size leaves is not descended: its leaves are tested in order
     auto is_range = [&](int ref) { return ref >= 0 && (n_leaves == 1 || s.nodes[ref].count <= s.leaf_size); };
     for (;;) {
@@ -746,7 +769,9 @@ static bool trace_any(const orc_scene& s, const Ray& r, int mode, Counters& c) {
     int stack[128];
     int sp = 0;
     int cur = 0;
-    const int n_leaves = (int)s.leaf_prim.size();
+    const int n_leaves = s.n_tree;
+    for (int j = s.n_tree; j < (int)s.leaf_prim.size(); j++)
+        if (test(s.leaf_prim[j])) return true;
     auto is_range = [&](int ref) { return ref >= 0 && (n_leaves == 1 || s.nodes[ref].count <= s.leaf_size); };
     for (;;) {
         if (cur < 0) {

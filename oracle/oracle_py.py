@@ -187,7 +187,12 @@ class OracleScene:
     def bvh_download(self):
         self.build_bvh()
         n = self.n_prims
-        ni = max(n - 1, 1)
+        class _Info(C.Structure):   # rtw_bvh_info (include/rtw.h)
+            _fields_ = [("n_leaves", C.c_int32), ("n_internal", C.c_int32), ("root", C.c_int32), ("n_top", C.c_int32),
+                        ("scene_min", C.c_float * 3), ("scene_max", C.c_float * 3)]
+        info = _Info()
+        assert lib().orc_bvh_info(self._h, C.byref(info)) == 0
+        ni = info.n_internal     # n - 1, less the primitives of the oversize list (csrc/device/lbvh.h)
         morton = np.zeros(n, np.uint64)
         leaf_prim = np.zeros(n, np.int32)
         left = np.zeros(ni, np.int32)

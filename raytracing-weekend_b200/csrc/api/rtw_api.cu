@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <algorithm>
 #include "rtw_ctx.h"
+#include "../device/lbvh.h"
 
 #include <cstring>
 
@@ -352,12 +353,12 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     if (!b.box_mn) {  // first build for this scene: allocate
         RTW_CUDA(c, dalloc(pool, &b.box_mn, n));
         RTW_CUDA(c, dalloc(pool, &b.box_mx, n));
-        RTW_CUDA(c, dalloc(pool, &b.bounds, 8));
+        RTW_CUDA(c, dalloc(pool, &b.bounds, 16));
         RTW_CUDA(c, dalloc(pool, &b.keys[0], n));
         RTW_CUDA(c, dalloc(pool, &b.keys[1], n));
         RTW_CUDA(c, dalloc(pool, &b.vals[0], n));
         RTW_CUDA(c, dalloc(pool, &b.vals[1], n));
-        RTW_CUDA(c, dalloc(pool, &b.hist, (size_t)256 * sort_num_blocks(n) + 1024));
+        RTW_CUDA(c, dalloc(pool, &b.hist, sort_scratch_words(n)));
         RTW_CUDA(c, dalloc(pool, &b.parent, ni));
         RTW_CUDA(c, dalloc(pool, &b.leaf_parent, n));
         RTW_CUDA(c, dalloc(pool, &b.flags, ni));
@@ -384,7 +385,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     RTW_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));
     RTW_CUDA(c, lbvh_build(c->stream, b, &launches));
     RTW_CUDA(c, cudaEventRecord(c->ev_end, c->stream));
-    uint32_t hb[8];
+    uint32_t hb[16];   // lbvh.cu k_bounds_init: scene box, n_top, centroid bounds, primitives flagged oversize
     RTW_CUDA(c, cudaMemcpyAsync(hb, b.bounds, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
     RTW_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f;
@@ -402,14 +403,19 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     sc.prim_ext = b.prim_ext;
     sc.leaf_prim = b.leaf_prim;
     sc.leaf_mat = b.leaf_mat;
+    // oversize primitives (device/lbvh.h): the hierarchy covers the first n_tree leaves, every ray tests the rest directly
+    const int n_tree = tree_leaf_count(n, (int)hb[14]);
+    const int ni_tree = n_tree > 1 ? n_tree - 1 : 1;
     sc.n_leaves = n;
-    sc.n_internal = ni;
+    sc.n_internal = ni_tree;
+    sc.over_first = n_tree;
+    sc.over_count = n > b.leaf_size ? n - n_tree : 0;   // a one-range scene walks all its leaves anyway
     sc.n_top = (int)hb[6];
     sc.wide = b.wide;
     if (wide) sc.n_top = 0;   // the wide walk reads its 128-byte records through L1 (no shared-memory staging)
     if (n <= b.leaf_size) sc.root = leaf_range_ref(0, n);
     else sc.root = sc.n_top > 0 ? (RTW_REF_TOP | 0u) : 0u;
-    c->n_internal = ni;
+    c->n_internal = ni_tree;
     // Traversal variant (tools/sweep_walk.sh, B200, 64 spp): persistent walkers win on the deep
     // hierarchy of the Book-2 scene (3410 primitives: k_traverse 0.77 -> 0.60 ms per 2 M rays) but
     // lose ~10 % on the 520-528 primitive scenes, where rays finish within a few steps of each other and

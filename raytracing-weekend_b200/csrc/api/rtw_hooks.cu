@@ -161,7 +161,7 @@ extern "C" int rtw_sort_pairs(rtw_ctx* c, uint64_t* keys, uint32_t* values, int 
     RTW_CUDA(c, dalloc(t.pool, &k[1], n));
     RTW_CUDA(c, dalloc(t.pool, &v[0], n));
     RTW_CUDA(c, dalloc(t.pool, &v[1], n));
-    RTW_CUDA(c, dalloc(t.pool, &hist, (size_t)256 * sort_num_blocks(n) + 1024));
+    RTW_CUDA(c, dalloc(t.pool, &hist, sort_scratch_words(n)));
     RTW_CUDA(c, cudaMemcpyAsync(k[0], keys, sizeof(uint64_t) * n, cudaMemcpyHostToDevice, c->stream));
     RTW_CUDA(c, cudaMemcpyAsync(v[0], values, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, c->stream));
     RTW_CUDA(c, sort_pairs(c->stream, k, v, n, hist, nullptr));

@@ -69,6 +69,8 @@ struct DScene {
     const float4* xforms;       // 6 float4 per transform: world→object rows 0-2, object→world rows 0-2
     uint32_t root;              // child reference of the root
     int n_leaves, n_internal, n_top;
+    int over_first, over_count; // oversize primitives (lbvh.h): leaves [over_first, over_first + over_count) are outside the
+                                // hierarchy and tested by every ray before it walks; over_count == 0: none
     int has_media;              // scene contains constant media (ray seed needed in traversal)
     int has_motion;             // scene contains moving spheres (gather time needed by shadow rays)
     int has_images;             // scene contains image textures (sphere uv needed)

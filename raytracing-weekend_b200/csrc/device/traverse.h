@@ -141,6 +141,21 @@ RTW_HD bool traverse_closest(const DScene& sc, const float4* top, const RayW& r,
     bool found = false;
     float tb = r.tmax;
     uint32_t lb = RTW_REF_NONE;
+    // the oversize primitives (lbvh.h) are outside the hierarchy: tested first, by every ray — a warp-uniform loop,
+    // and an early limit tb for the walk
+    for (uint32_t leaf = (uint32_t)sc.over_first, end = leaf + (uint32_t)sc.over_count; leaf < end; leaf++) {
+        float t;
+        if (kStats) stats->prims++;
+        if (prim_candidate(SrcScene<Mem>{sc}, leaf, r, xfc, t)) {
+            if (!found || t < tb) {
+                found = true;
+                tb = t;
+                lb = leaf;
+            } else if (t == tb && leaf_prim_of(sc, leaf) < leaf_prim_of(sc, lb)) {
+                lb = leaf;
+            }
+        }
+    }
     for (;;) {
         bool exhausted = false;
         while (!(cur & RTW_REF_LEAF)) {
@@ -206,6 +221,11 @@ RTW_HD bool traverse_any(const DScene& sc, const float4* top, const RayW& r, Tra
     uint32_t stack[RTW_STACK];
     int sp = 0;
     uint32_t cur = sc.root;
+    for (uint32_t leaf = (uint32_t)sc.over_first, end = leaf + (uint32_t)sc.over_count; leaf < end; leaf++) {   // oversize list first
+        float t;
+        if (kStats) stats->prims++;
+        if (prim_candidate(SrcScene<Mem>{sc}, leaf, r, xfc, t)) return true;
+    }
     for (;;) {
         bool exhausted = false;
         while (!(cur & RTW_REF_LEAF)) {
@@ -403,13 +423,18 @@ struct Walker {
     // the stack lives OUTSIDE the struct (a dynamically indexed member would force every field
     // of the walker into local memory); the caller owns `uint32_t stack[RTW_STACK]`
 
-    RTW_HD void begin(const DScene& sc, const RayW& ray) {
+    RTW_HD void begin(const DScene& sc, const RayW& ray, uint32_t* stack) {
         r = ray;
         if (!(sc.root & RTW_REF_LEAF)) sr = make_slab_ray(r);
         xfc.xf = -1;
         cur = sc.root;
         li = lend = 0;
         sp = 0;
+        if (sc.over_count > 0) {   // the oversize list (lbvh.h) is the first range in progress; the root waits on the stack
+            li = (uint32_t)sc.over_first;
+            lend = li + (uint32_t)sc.over_count;
+            stack[sp++] = sc.root;
+        }
         tb = r.tmax;
         lb = RTW_REF_NONE;
         found = false;

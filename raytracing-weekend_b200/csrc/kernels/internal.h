@@ -10,9 +10,10 @@ namespace rtw {
 // ---- radix sort (kernels/sort.cu) -----------------------------------------
 // Stable LSD radix sort of (64-bit key, 32-bit value) pairs, 8 passes of 8 bits.
 // keys/vals are ping-pong buffers of n elements each; the sorted result ends in
-// keys[0]/vals[0].  hist must hold 256 * sort_num_blocks(n) + 1024 uint32.
-int  sort_num_blocks(int n);
-cudaError_t sort_pairs(cudaStream_t s, unsigned long long* keys[2], uint32_t* vals[2], int n, uint32_t* hist,
+// keys[0]/vals[0].  scratch must hold sort_scratch_words(n) uint32 (digit histograms, tile tickets, the
+// look-back status words of the tiles); sort_pairs clears it itself.
+size_t sort_scratch_words(int n);
+cudaError_t sort_pairs(cudaStream_t s, unsigned long long* keys[2], uint32_t* vals[2], int n, uint32_t* scratch,
                        uint64_t* launches);
 
 // ---- LBVH build (kernels/lbvh.cu) -------------------------------------------

@@ -27,10 +27,11 @@ __device__ __forceinline__ float dec_f(uint32_t u) {
     return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
+// bounds[0..5] scene box (encoded min xyz, max xyz), [6] n_top, [8..13] bounds of the box centroids,
+// [14] primitives flagged oversize (lbvh.h); 16 words
 __global__ void k_bounds_init(uint32_t* bounds) {
-    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;        // min
-    else if (threadIdx.x < 6) bounds[threadIdx.x] = 0u;            // max
-    else if (threadIdx.x < 8) bounds[threadIdx.x] = 0u;            // [6] = n_top
+    const int t = threadIdx.x & 7;
+    if (threadIdx.x < 16) bounds[threadIdx.x] = t < 3 ? 0xffffffffu : 0u;   // min words start at the top, everything else at 0
 }
 
 __global__ void __launch_bounds__(kThreads) k_prim_aabb(const rtw_prim* __restrict__ prims,
@@ -38,44 +39,65 @@ __global__ void __launch_bounds__(kThreads) k_prim_aabb(const rtw_prim* __restri
                                                          float4* __restrict__ box_mn, float4* __restrict__ box_mx,
                                                          uint32_t* __restrict__ bounds) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float3 mn = f3(RTW_FLT_MAX), mx = f3(-RTW_FLT_MAX);
+    // v[0..2] min, v[3..5] max of the boxes; v[6..8] min, v[9..11] max of the box centroids
+    float v[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) v[k] = (k % 6) < 3 ? RTW_FLT_MAX : -RTW_FLT_MAX;
     if (i < n) {
         const Box3 b = prim_world_aabb(prims[i], xforms);
         box_mn[i] = make_float4(b.mn.x, b.mn.y, b.mn.z, 0.f);
         box_mx[i] = make_float4(b.mx.x, b.mx.y, b.mx.z, 0.f);
-        mn = b.mn;
-        mx = b.mx;
+        const float3 c = box_centroid(b);
+        v[0] = b.mn.x; v[1] = b.mn.y; v[2] = b.mn.z; v[3] = b.mx.x; v[4] = b.mx.y; v[5] = b.mx.z;
+        v[6] = c.x; v[7] = c.y; v[8] = c.z; v[9] = c.x; v[10] = c.y; v[11] = c.z;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        mn.x = fminf(mn.x, __shfl_xor_sync(0xffffffffu, mn.x, o));
-        mn.y = fminf(mn.y, __shfl_xor_sync(0xffffffffu, mn.y, o));
-        mn.z = fminf(mn.z, __shfl_xor_sync(0xffffffffu, mn.z, o));
-        mx.x = fmaxf(mx.x, __shfl_xor_sync(0xffffffffu, mx.x, o));
-        mx.y = fmaxf(mx.y, __shfl_xor_sync(0xffffffffu, mx.y, o));
-        mx.z = fmaxf(mx.z, __shfl_xor_sync(0xffffffffu, mx.z, o));
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            const float u = __shfl_xor_sync(0xffffffffu, v[k], o);
+            v[k] = (k % 6) < 3 ? fminf(v[k], u) : fmaxf(v[k], u);
+        }
     }
-    if ((threadIdx.x & 31) == 0) {
-        atomicMin(bounds + 0, enc_f(mn.x));
-        atomicMin(bounds + 1, enc_f(mn.y));
-        atomicMin(bounds + 2, enc_f(mn.z));
-        atomicMax(bounds + 3, enc_f(mx.x));
-        atomicMax(bounds + 4, enc_f(mx.y));
-        atomicMax(bounds + 5, enc_f(mx.z));
+    // one set of atomics per CTA, not per warp: at 2^20 primitives 32768 warps x 6 atomics on the same six words
+    // were 140 us of serialised read-modify-writes (profiles/r02/build_r02f.md)
+    __shared__ float s_b[kThreads / 32][12];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 12; k++) s_b[warp][k] = v[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int k = threadIdx.x;
+        const bool is_min = (k % 6) < 3;
+        float r = s_b[0][k];
+#pragma unroll
+        for (int w = 1; w < kThreads / 32; w++) r = is_min ? fminf(r, s_b[w][k]) : fmaxf(r, s_b[w][k]);
+        uint32_t* word = bounds + (k < 6 ? k : k + 2);
+        if (is_min) atomicMin(word, enc_f(r));
+        else atomicMax(word, enc_f(r));
     }
 }
 
 __global__ void __launch_bounds__(kThreads) k_morton(const float4* __restrict__ box_mn, const float4* __restrict__ box_mx,
-                                                      int n, const uint32_t* __restrict__ bounds,
+                                                      int n, uint32_t* bounds,
                                                       unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float3 lo = f3(dec_f(bounds[0]), dec_f(bounds[1]), dec_f(bounds[2]));
     const float3 hi = f3(dec_f(bounds[3]), dec_f(bounds[4]), dec_f(bounds[5]));
+    const float3 clo = f3(dec_f(bounds[8]), dec_f(bounds[9]), dec_f(bounds[10]));
+    const float3 chi = f3(dec_f(bounds[11]), dec_f(bounds[12]), dec_f(bounds[13]));
     Box3 b;
     b.mn = f3(box_mn[i]);
     b.mx = f3(box_mx[i]);
-    keys[i] = morton63(b, lo, hi - lo);
+    unsigned long long key = morton63(b, lo, hi - lo);
+    if (box_is_oversize(b, clo, chi)) {   // sorts behind every other key (lbvh.h "oversize primitives")
+        key |= RTW_KEY_OVERSIZE;
+        atomicAdd(bounds + 14, 1u);
+    }
+    keys[i] = key;
     vals[i] = (uint32_t)i;
 }
 
@@ -102,11 +124,13 @@ __global__ void __launch_bounds__(kThreads) k_pack_leaves(const rtw_prim* __rest
     leaf_mx[j] = box_mx[pi];
 }
 
-__global__ void __launch_bounds__(kThreads) k_karras(const unsigned long long* __restrict__ keys, int n,
+__global__ void __launch_bounds__(kThreads) k_karras(const unsigned long long* __restrict__ keys, int n_all,
+                                                      const uint32_t* __restrict__ bounds,
                                                       float4* __restrict__ nodes, int* __restrict__ parent,
                                                       int* __restrict__ leaf_parent, int* __restrict__ flags,
                                                       int* __restrict__ top_index, int leaf_size) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = tree_leaf_count(n_all, (int)bounds[14]);   // the hierarchy covers the leaves in front of the oversize list
     if (i >= n - 1) return;
     int left, right, lo, gamma, hi;
     karras_node(keys, n, i, left, right, lo, gamma, hi);
@@ -150,11 +174,12 @@ __device__ __forceinline__ void child_box(uint32_t ref, const float4* leaf_mn, c
     }
 }
 
-__global__ void __launch_bounds__(kThreads) k_refit(int n, const int* __restrict__ leaf_parent, const int* __restrict__ parent,
+__global__ void __launch_bounds__(kThreads) k_refit(int n_all, const uint32_t* __restrict__ bounds,
+                                                     const int* __restrict__ leaf_parent, const int* __restrict__ parent,
                                                      int* flags, const float4* __restrict__ leaf_mn,
                                                      const float4* __restrict__ leaf_mx, float4* nodes) {
     const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
-    if (leaf >= n) return;
+    if (leaf >= tree_leaf_count(n_all, (int)bounds[14])) return;
     int cur = leaf_parent[leaf];
     while (cur >= 0) {
         if (atomicAdd(flags + cur, 1) == 0) return;  // first arrival stops, second computes
@@ -218,9 +243,10 @@ __global__ void __launch_bounds__(kThreads) k_build_top(const float4* __restrict
 }
 
 // 4-wide nodes derived from the refitted two-child nodes: one thread per internal node
-__global__ void __launch_bounds__(kThreads) k_widen(const float4* __restrict__ nodes, int n_internal, float4* __restrict__ wide) {
+__global__ void __launch_bounds__(kThreads) k_widen(const float4* __restrict__ nodes, int n_all, const uint32_t* __restrict__ bounds,
+                                                     float4* __restrict__ wide) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_internal) return;
+    if (i >= tree_leaf_count(n_all, (int)bounds[14]) - 1) return;
     float4 w[8];
     make_wide_node(nodes, i, w);
 #pragma unroll
@@ -252,17 +278,22 @@ cudaError_t lbvh_build(cudaStream_t s, const BuildBuffers& b, uint64_t* launches
     } else {
         n_internal = n - 1;
         const int nbi = (n_internal + kThreads - 1) / kThreads;
-        k_karras<<<nbi, kThreads, 0, s>>>(b.keys[0], n, b.nodes, b.parent, b.leaf_parent, b.flags, b.top_index,
+        k_karras<<<nbi, kThreads, 0, s>>>(b.keys[0], n, b.bounds, b.nodes, b.parent, b.leaf_parent, b.flags, b.top_index,
                                           b.leaf_size < 1 ? 1 : (b.leaf_size > RTW_MAX_LEAF_SIZE ? RTW_MAX_LEAF_SIZE : b.leaf_size));
-        k_refit<<<nb, kThreads, 0, s>>>(n, b.leaf_parent, b.parent, b.flags, b.leaf_mn, b.leaf_mx, b.nodes);
+        k_refit<<<nb, kThreads, 0, s>>>(n, b.bounds, b.leaf_parent, b.parent, b.flags, b.leaf_mn, b.leaf_mx, b.nodes);
         l += 2;
     }
-    const int max_top = b.max_top < n_internal ? b.max_top : n_internal;
-    k_build_top<<<1, kThreads, sizeof(int) * (max_top > 0 ? max_top : 1), s>>>(b.nodes, n_internal, max_top, b.top_index,
-                                                                              b.top_nodes, b.bounds + 6);
-    l += 1;
+    // the shared-memory top table is for the two-child walk only (the wide walk reads its 128-byte records through
+    // L1): its breadth-first numbering is one thread's loop — 0.67 ms for 1024 nodes — and is skipped when unused
+    // (bounds[6] = n_top stays 0 from k_bounds_init)
+    if (!b.wide) {
+        const int max_top = b.max_top < n_internal ? b.max_top : n_internal;
+        k_build_top<<<1, kThreads, sizeof(int) * (max_top > 0 ? max_top : 1), s>>>(b.nodes, n_internal, max_top, b.top_index,
+                                                                                  b.top_nodes, b.bounds + 6);
+        l += 1;
+    }
     if (b.wide) {
-        k_widen<<<(n_internal + kThreads - 1) / kThreads, kThreads, 0, s>>>(b.nodes, n_internal, b.wide);
+        k_widen<<<(n_internal + kThreads - 1) / kThreads, kThreads, 0, s>>>(b.nodes, n, b.bounds, b.wide);
         l += 1;
     }
     if (launches) *launches += l;

@@ -247,7 +247,7 @@ __device__ __forceinline__ void walk_persistent(const DScene& sc, const DWave* w
             if (idx < total) {
                 RayW r;
                 if (job.load(idx, r)) {
-                    wk.begin(sc, r);
+                    wk.begin(sc, r, stack);
                     active = true;
                     item = idx;
                 }

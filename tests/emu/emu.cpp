@@ -132,8 +132,16 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
     }
     e->scene_min[0] = lo.x; e->scene_min[1] = lo.y; e->scene_min[2] = lo.z;
     e->scene_max[0] = hi.x; e->scene_max[1] = hi.y; e->scene_max[2] = hi.z;
+    float3 clo = f3(RTW_FLT_MAX), chi = f3(-RTW_FLT_MAX);   // bounds of the box centroids (k_prim_aabb)
+    for (int i = 0; i < n; i++) { clo = vmin(clo, box_centroid(boxes[i])); chi = vmax(chi, box_centroid(boxes[i])); }
     std::vector<std::pair<unsigned long long, int>> kv(n);
-    for (int i = 0; i < n; i++) kv[i] = {morton63(boxes[i], lo, hi - lo), i};
+    int flagged = 0;
+    for (int i = 0; i < n; i++) {   // k_morton: oversize primitives sort behind everything else (lbvh.h)
+        unsigned long long key = morton63(boxes[i], lo, hi - lo);
+        if (box_is_oversize(boxes[i], clo, chi)) { key |= RTW_KEY_OVERSIZE; flagged++; }
+        kv[i] = {key, i};
+    }
+    const int n_all = n;
     std::stable_sort(kv.begin(), kv.end(), [](const auto& a, const auto& b) { return a.first < b.first; });  // stands in for sort.cu
     e->keys.resize(n);
     e->leaf_prim.resize(n); e->leaf_mat.resize(n);
@@ -149,7 +157,8 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
         e->leaf_mn[j] = make_float4(boxes[pi].mn.x, boxes[pi].mn.y, boxes[pi].mn.z, 0.f);
         e->leaf_mx[j] = make_float4(boxes[pi].mx.x, boxes[pi].mx.y, boxes[pi].mx.z, 0.f);
     }
-    const int ni = n > 1 ? n - 1 : 1;
+    const int m = tree_leaf_count(n_all, flagged);   // leaves under the hierarchy; [m, n) is the oversize list
+    const int ni = m > 1 ? m - 1 : 1;
     e->nodes.assign((size_t)4 * ni, make_float4(0, 0, 0, 0));
     e->left.assign(ni, 0); e->right.assign(ni, 0);
     std::vector<int> parent(ni, -1), leaf_parent(n, -1), flags(ni, 0);
@@ -163,7 +172,7 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
     } else {
         for (int i = 0; i < ni; i++) {
             int l, r, lo, gamma, hi;
-            karras_node(e->keys.data(), n, i, l, r, lo, gamma, hi);
+            karras_node(e->keys.data(), m, i, l, r, lo, gamma, hi);
             e->left[i] = l; e->right[i] = r;
             if (l < 0) leaf_parent[~l] = i; else parent[l] = i;
             if (r < 0) leaf_parent[~r] = i; else parent[r] = i;
@@ -179,7 +188,7 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
                 mx = vmax(f3(n0.w, n1.x, n1.y), f3(n2.y, n2.z, n2.w));
             }
         };
-        for (int leaf = 0; leaf < n; leaf++) {  // k_refit, sequentialised
+        for (int leaf = 0; leaf < m; leaf++) {  // k_refit, sequentialised
             int cur = leaf_parent[leaf];
             while (cur >= 0) {
                 if (flags[cur]++ == 0) break;
@@ -226,6 +235,8 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
     sc.leaf_mat = e->leaf_mat.data();
     sc.n_leaves = n;
     sc.n_internal = ni;
+    sc.over_first = m;
+    sc.over_count = n > leaf_size ? n - m : 0;
     sc.n_top = (int)queue.size();
     // max_top < 0: walk the 4-wide nodes (k_widen in loop form), as rtw_build_accel does by default
     if (max_top < 0 && n > leaf_size) {
@@ -240,6 +251,8 @@ extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) 
 }
 
 extern "C" void emu_destroy(Emu* e) { delete e; }
+
+extern "C" int emu_n_internal(const Emu* e) { return e->sc.n_internal; }
 
 extern "C" void emu_bvh_download(const Emu* e, unsigned long long* morton, int* leaf_prim, int* left, int* right,
                                  float* bounds, float* scene_box) {

@@ -41,6 +41,8 @@ def lib():
     L.emu_create.argtypes = [vp, i32, i32]
     L.emu_destroy.argtypes = [vp]
     L.emu_bvh_download.argtypes = [vp] * 7
+    L.emu_n_internal.restype = i32
+    L.emu_n_internal.argtypes = [vp]
     L.emu_trace.argtypes = [vp, vp, i32, vp, vp, vp, vp]
     L.emu_render.restype = i32
     L.emu_render.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, vp, vp]
@@ -73,7 +75,7 @@ class EmuScene:
             pass
 
     def bvh_download(self):
-        n, ni = self.n, max(self.n - 1, 1)
+        n, ni = self.n, int(lib().emu_n_internal(self._h))
         morton = np.zeros(n, np.uint64)
         leaf_prim = np.zeros(n, np.int32)
         left = np.zeros(ni, np.int32)

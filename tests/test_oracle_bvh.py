@@ -34,16 +34,23 @@ def test_lbvh_mirror_invariants(rtw, orc):
     morton, leaf_prim, left, right, bounds = o.bvh_download()
     assert np.all(morton[:-1] <= morton[1:])                 # sortedness
     assert sorted(leaf_prim.tolist()) == list(range(n))      # permutation
-    # every internal node except the root and every leaf is referenced exactly once
-    refs = np.concatenate([left, right])
-    assert sorted(refs[refs >= 0].tolist()) == list(range(1, n - 1))
-    assert sorted((~refs[refs < 0]).tolist()) == list(range(n))
-    # children boxes contain the leaf boxes below them (spot check: direct leaf children)
+    # the oversize list (csrc/device/lbvh.h): the r = 5000 shell and the r = 500 fog sphere (scene/ioScene.h:838,931) carry
+    # key bit 63, sort last and stay outside the hierarchy, which covers the other m = n - 2 leaves
+    m = len(left) + 1
+    assert m == n - 2 and np.all(morton[m:] >> np.uint64(63) == 1) and np.all(morton[:m] >> np.uint64(63) == 0)
     aabb = o.prim_aabbs()
-    for i in range(n - 1):
+    assert sorted((aabb[leaf_prim[m:], 3] - aabb[leaf_prim[m:], 0]).round().tolist()) == [1000.0, 10000.0]
+    # every internal node except the root and every leaf under the hierarchy is referenced exactly once
+    refs = np.concatenate([left, right])
+    assert sorted(refs[refs >= 0].tolist()) == list(range(1, m - 1))
+    assert sorted((~refs[refs < 0]).tolist()) == list(range(m))
+    # children boxes contain the leaf boxes below them (spot check: direct leaf children)
+    for i in range(m - 1):
         for ref, b in ((left[i], bounds[i, :6]), (right[i], bounds[i, 6:])):
             if ref < 0:
                 assert np.array_equal(b, aabb[leaf_prim[~ref]])
+    # without the two giants no box of the hierarchy is larger than the rest of the scene
+    assert float(np.abs(bounds).max()) < 1100.0
     s.close()
 
 
