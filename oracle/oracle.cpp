@@ -1,4 +1,5 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.h).  PARITY UNPINNED except RNG.
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.h).  Parity PINNED to the reference compiled for the host
+// (oracle/_ref, tests/golden/ref_frames.npz, tests/test_ref_pin.py): scenes 0-4 and three hand-built scenes, bit for bit.
 //
 // Scalar CPU restatement of the reference launch.  One function per reference
 // program; citations are relative to /root/reference/RestOfLife/.

@@ -6,12 +6,15 @@
  * --impl reference legs may load this library.  The product
  * (raytracing-weekend_b200/) never includes, links or calls anything in oracle/.
  *
- * PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for
- * this path and none of its device code compiles here (every file needs optix.h,
- * SURVEY.md §8c).  The only source-pinned pieces are tea<N>/xorshift32/randf
- * (lib/random.cuh compiles standalone; KATs in tests/golden/rng_kat.json were
- * produced by compiling THAT file, see oracle/ref_rng_kat.sh).  Everything else
- * is a statement-by-statement restatement, each function citing file:line.
+ * PARITY PINNED (round 2).  The reference ships no tests, golden vectors or fixtures for this path and its device
+ * code needs optix.h — but its SOURCES compile for the host against the stand-in headers of oracle/ref_shim
+ * (`make -C oracle ref` -> oracle/_ref/{ref_cli, libref.so, libref_dm.so, ref_rng}; nothing is copied).  The frames the
+ * reference's own programs render there (scenes 0-4 through Director::init -> createScene -> renderFrame, plus three
+ * hand-built scenes for the branches no built-in scene reaches) are committed as tests/golden/ref_frames.npz by
+ * tests/golden/make_ref_golden.py, and tests/test_ref_pin.py asserts this oracle reproduces them BIT FOR BIT; tea /
+ * xorshift32 / randf are pinned by lib/random.cuh compiled alone (tests/golden/rng_kat.json).  What the stand-in
+ * decides where OptiX leaves a choice to the driver is listed at the top of oracle/ref_shim/optix.h.  Every function
+ * below cites the reference file:line it restates.
  *
  * The scene description consumed here is the C-ABI POD of include/rtw.h.
  */

@@ -112,7 +112,17 @@ static int for_each_gpu(rtw_multi* m, F fn) {
     return RTW_OK;
 }
 
+// The multi-GPU entry points hop between devices on the CALLER's thread (allocation, peer set-up, tear-down); the
+// caller's current device is put back when they return (a host that also uses the CUDA runtime itself — PyTorch in the
+// tests — would otherwise find its allocations landing on the last GPU of the list).
+struct DeviceGuard {
+    int dev = -1;
+    DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { dev = -1; cudaGetLastError(); } }
+    ~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
+};
+
 extern "C" int rtw_create_multi(const int* devices, int n, rtw_multi** out) {
+    DeviceGuard restore_callers_device;
     if (!devices || n < 1 || n > 64 || !out) return RTW_ERR_INVALID;
     rtw_multi* m = new rtw_multi();
     m->devices.assign(devices, devices + n);
@@ -153,6 +163,7 @@ extern "C" int rtw_create_multi(const int* devices, int n, rtw_multi** out) {
 }
 
 extern "C" int rtw_multi_destroy(rtw_multi* m) {
+    DeviceGuard restore_callers_device;
     if (!m) return RTW_ERR_INVALID;
     for (size_t g = 0; g < m->ctx.size(); g++) {
         cudaSetDevice(m->devices[g]);
@@ -172,6 +183,7 @@ extern "C" int rtw_multi_device_count(const rtw_multi* m) { return m ? (int)m->c
 extern "C" int rtw_multi_uses_nccl(const rtw_multi* m) { return (m && m->use_nccl) ? 1 : 0; }
 
 extern "C" int rtw_multi_set_option(rtw_multi* m, const char* name, int64_t value) {
+    DeviceGuard restore_callers_device;
     if (!m || !name) return RTW_ERR_INVALID;
     if (!strcmp(name, "shard")) {
         if (value < 0 || value > 2) return mfail(m, RTW_ERR_INVALID, "shard out of range [0, 2] (0 = auto, 1 = samples, 2 = tiles)");
@@ -186,10 +198,12 @@ extern "C" int rtw_multi_set_option(rtw_multi* m, const char* name, int64_t valu
 }
 
 extern "C" int rtw_multi_upload_scene(rtw_multi* m, const rtw_scene_desc* scene) {
+    DeviceGuard restore_callers_device;
     if (!m || !scene) return RTW_ERR_INVALID;
     return for_each_gpu(m, [&](int g) { return rtw_upload_scene(m->ctx[g], scene); });
 }
 extern "C" int rtw_multi_build_accel(rtw_multi* m) {
+    DeviceGuard restore_callers_device;
     if (!m) return RTW_ERR_INVALID;
     return for_each_gpu(m, [&](int g) { return rtw_build_accel(m->ctx[g]); });
 }
@@ -224,6 +238,7 @@ static inline void tile_rows(int Ny, int g, int G, int& first, int& count) {
 }
 
 extern "C" int rtw_multi_render(rtw_multi* m, int Nx, int Ny, int spp, int max_depth, float* rgba_out_host) {
+    DeviceGuard restore_callers_device;
     if (!m) return RTW_ERR_INVALID;
     if (!rgba_out_host || spp <= 0 || Nx <= 0 || Ny <= 0 || (unsigned long long)Nx * (unsigned long long)Ny > 0x7fffffffull)
         return mfail(m, RTW_ERR_INVALID, "bad render arguments");
@@ -338,6 +353,7 @@ extern "C" int rtw_multi_render(rtw_multi* m, int Nx, int Ny, int spp, int max_d
 }
 
 extern "C" int rtw_multi_get_linear(rtw_multi* m, float* rgba_linear_mean_host, int n_floats, int spp) {
+    DeviceGuard restore_callers_device;
     if (!m || !rgba_linear_mean_host || spp <= 0) return RTW_ERR_INVALID;
     if (n_floats != m->frame_pixels * 4) return mfail(m, RTW_ERR_INVALID, "n_floats != Nx*Ny*4");
     cudaSetDevice(m->devices[0]);

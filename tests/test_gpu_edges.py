@@ -210,3 +210,41 @@ def test_coincident_primitives_do_not_overflow_the_traversal_stack(director, rtw
         assert director.stats()["stack_overflows"] == 0
     finally:
         director.set_option("leaf_size", 0)
+
+
+def test_subnormal_radiance_is_flushed_by_the_accumulator_atomics(director, rtw, orc):
+    """The one place where the device does NOT keep the oracle's bits: finished paths are added to the
+    accumulator with red/atom.global.add.v4.f32 (k_regen.sass: ATOMG.E.ADD.F32x4.FTZ.RN), and fp32 atomic adds on global
+    memory flush subnormal inputs and results to zero — an architectural property of the instruction.  Cornell box
+    with the light's radiance scaled to 1e-39: every path radiance is subnormal; the oracle keeps the sums, the device
+    returns exactly 0 for them.  Normal-range sums are untouched (every other test)."""
+    s = rtw.Scene(0, 48, 48)
+    d1 = rtw.SceneDesc.from_buffer_copy(s.desc.contents)
+    texs = (rtw.Texture * d1.n_textures)(*[d1.textures[i] for i in range(d1.n_textures)])
+    lights = (rtw.Light * d1.n_lights)(*[d1.lights[i] for i in range(d1.n_lights)])
+    scaled = 0
+    for t in texs:
+        if t.type == 1 and max(t.color) > 1.0:          # RTW_TEX_CONSTANT: the emitter's colour (15, 15, 15)
+            for k in range(3):
+                t.color[k] = 1e-39
+            scaled += 1
+    for l in lights:
+        for k in range(3):
+            l.emission[k] = 1e-39
+    assert scaled == 1 and d1.n_lights == 1
+    d1.textures = C.cast(texs, C.POINTER(rtw.Texture))
+    d1.lights = C.cast(lights, C.POINTER(rtw.Light))
+    p1 = C.pointer(d1)
+    director.init(48, 48, 1)
+    director.scene = s
+    director.upload(p1)
+    o = orc.OracleScene(p1, d1.n_prims)
+    ref, c = o.render(48, 48, 1, mode=0)
+    director.renderFrame(1)
+    got = director.linear()
+    assert director.stats()["rays_closest"] == c["rays_closest"] and director.stats()["rays_shadow"] == c["rays_shadow"]   # the same walks
+    rgb_ref, rgb_got = ref[..., :3], got[..., :3]
+    tiny = np.abs(rgb_ref) < np.float32(1.1754944e-38)
+    assert tiny.all() and (rgb_ref != 0).mean() > 0.3          # the oracle's frame is lit, and all of it is subnormal
+    assert np.all(rgb_got == 0.0)                               # ... the device flushed every one of those sums
+    assert np.array_equal(ref[..., 3], got[..., 3])             # sample counts are ordinary numbers

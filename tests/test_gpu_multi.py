@@ -74,7 +74,7 @@ def test_rows_entry_point_renders_only_its_rows(director, rtw, orc):
     Nx, Ny = 64, 40
     director.init(Nx, Ny, 1)
     director.createScene(3)
-    acc = torch.full((Ny, Nx, 4), -7.0, device="cuda")
+    acc = torch.full((Ny, Nx, 4), -7.0, device="cuda:0")   # the context of the `director` fixture is on GPU 0
     L = rtw.lib()
     assert L.rtw_render_accum_rows(director._c, Nx, Ny, 10, 17, 0, 1, 1, 20, acc.data_ptr()) == rtw.RTW_OK
     got = acc.cpu().numpy()
