@@ -500,6 +500,22 @@ def main():
                                     "same roof, `alone` the same kernel timed with one wave.  traffic = dram bytes of one launch from the committed "
                                     "ncu capture (traffic_source), C2 only" % waves,
                             "stages": stages}
+        # ---- the other roof of this path: instruction issue (C2) ----
+        # warp instructions of one steady-state iteration of one wave, from the committed ncu capture
+        # (smsp__inst_executed.sum per launch), scaled by the iterations the timed frames ran, against
+        # SMs x 4 schedulers x the SM clock sampled during the run.
+        wi = traffic_doc.get("warp_instructions_per_launch") if SCENE == 0 else None
+        clk_now = line["clocks"].get("sm_mhz") or 1965.0
+        if wi and not streaming:
+            per_iter = float(sum(wi.values()))
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            peak_issue = sms * 4 * clk_now * 1e6
+            achieved_issue = per_iter * iters / max(agg["render_ms"] * 1e-3, 1e-9)
+            line["roofline"]["issue"] = {"warp_instructions_per_wave_iteration": per_iter, "wave_iterations": iters,
+                                         "achieved": achieved_issue / 1e9, "peak": peak_issue / 1e9, "unit": "G warp-inst/s",
+                                         "frac": achieved_issue / peak_issue,
+                                         "note": "instructions from the committed capture (traffic_source), iterations and time from this run; "
+                                                 "with `step.frac` it says how far the frame is from BOTH of its roofs"}
         # ---- the on-chip (L1 / L2) stream of the traversal, from the ORACLE's visit counters ----
         try:
             s2, o2 = oracle_scene(rtw)

@@ -148,6 +148,13 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "tail_paths")) {
         if (value < 0 || value > (1 << 22)) return fail(c, RTW_ERR_INVALID, "tail_paths out of range [0, 2^22]");
         c->opt_tail_paths = (int)value;
+    } else if (!strcmp(name, "sort_rays")) {
+        if (value < -1 || value > 2) return fail(c, RTW_ERR_INVALID, "sort_rays out of range [-1, 2]");
+        c->opt_sort_rays = (int)value;
+    } else if (!strcmp(name, "sort_obits") || !strcmp(name, "sort_dbits")) {
+        if (value < 1 || value > 5) return fail(c, RTW_ERR_INVALID, "sort_obits / sort_dbits out of range [1, 5]");
+        if (name[5] == 'o') c->opt_sort_obits = (int)value;
+        else c->opt_sort_dbits = (int)value;   // (obits + dbits <= 6 is enforced where the bins are sized: the direction bits give way)
     } else if (!strcmp(name, "fuse_shadow")) {
         if (value < -1 || value > 1) return fail(c, RTW_ERR_INVALID, "fuse_shadow out of range [-1, 1]");
         c->opt_fuse_shadow = (int)value;
@@ -395,6 +402,8 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     for (int i = 0; i < 3; i++) {
         c->scene_min[i] = dec(hb[i]);
         c->scene_max[i] = dec(hb[3 + i]);
+        c->key_lo[i] = dec(hb[8 + i]);
+        c->key_hi[i] = dec(hb[11 + i]);
     }
     DScene& sc = c->scene;
     sc.nodes = b.nodes;

@@ -19,8 +19,22 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
         for (auto& e : wv.ev_iter) RTW_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         RTW_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&wv.h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8));
     }
-    if (wv.capacity >= P && wv.for_stream == stream) {
+    const int sort_rays = c->opt_sort_rays >= 0 ? c->opt_sort_rays : (c->cfg.has_shadow ? 1 : 0);   // -1 = auto (rtw_ctx.h)
+    const bool want_sort = sort_rays > 0 && !stream && c->cfg.walker && !c->cfg.small;
+    const int key_ob = c->opt_sort_obits, key_db = std::max(1, std::min(c->opt_sort_dbits, 6 - key_ob));   // at most 2^18 bins
+    const int key_bits = 3 * (key_ob + key_db);
+    auto set_key_cells = [&](DWave& w) {   // the ray keys' origin cells span the bounds of the primitive centroids
+        w.key_obits = key_ob;
+        w.key_dbits = key_db;
+        for (int k = 0; k < 3; k++) {
+            const float ext = c->key_hi[k] - c->key_lo[k];
+            (&w.key_lo.x)[k] = c->key_lo[k];
+            (&w.key_scale.x)[k] = ext > 0.f ? (float)(1 << c->opt_sort_obits) / ext : 0.f;
+        }
+    };
+    if (wv.capacity >= P && wv.for_stream == stream && (wv.w.bins != nullptr) == want_sort && (!want_sort || wv.key_bits == key_bits)) {
         wv.w.P = P;
+        set_key_cells(wv.w);
         return RTW_OK;
     }
     RTW_CUDA(c, cudaStreamSynchronize(wv.stream));
@@ -41,6 +55,13 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
         RTW_CUDA(c, dalloc(pool, &w.sh_c, P));
     }
     RTW_CUDA(c, dalloc(pool, &w.counters, RTW_C_WORDS));
+    if (want_sort) {
+        RTW_CUDA(c, dalloc(pool, &w.bins, ((size_t)1 << key_bits) + 1 + 256));   // counts / first positions, the total, the chunk sums
+        RTW_CUDA(c, dalloc(pool, &w.bin_rank, P));
+        RTW_CUDA(c, dalloc(pool, &w.order, P));
+        wv.key_bits = key_bits;
+    }
+    set_key_cells(w);
     w.P = P;
     wv.capacity = P;
     wv.for_stream = stream;
@@ -194,6 +215,7 @@ extern "C" int rtw_render_accum_rows(rtw_ctx* c, int Nx, int Ny, int row_first, 
             cudaEvent_t* sev = nullptr;
             if (j == 0 && c->opt_profile && sampled < kMaxSampled && r.iter % prof_stride == 0) sev = c->prof_events.data() + 5 * sampled++;
             LaunchCfg cfg = c->cfg;
+            cfg.sort_shadow = c->opt_sort_rays >= 2;   // (auto bins the closest-hit rays only)
             cfg.mid_event = nullptr;
             if (c->opt_stagger && r.iter == 0 && n_waves > 1) {
                 if ((j & 1) == 0 && j + 1 < n_waves) cfg.mid_event = wv.ev_done;

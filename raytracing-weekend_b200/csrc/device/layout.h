@@ -217,6 +217,16 @@ struct DWave {
     float4* sh_c;       //               contribution.xyz, path seed bits
     float4* sq;         // streaming wavefront: 2 buffers x 4 classes x 5 float4 arrays of P entries (device/stream.h)
     uint32_t* counters; // RTW_C_WORDS words
+    // Option sort_rays (LBVH walkers): a stage takes its rays bin by bin — bin = (origin cell, direction bin) — instead
+    // of in slot / queue order.  One counting sort per stage and iteration (kernels/wavefront.cu k_ray_bin, k_bin_scan,
+    // k_ray_place): bins[key] counts, then holds the first position of the bin; bin_rank[i] = (key, rank inside the bin)
+    // of item i; order[position] = item.  bins[n_bins] = number of items placed (empty slots are left out).
+    uint32_t* bins;             // n_bins + 1 + 256 words (the last 256: sums of 1024-bin chunks); nullptr = option off
+    uint2* bin_rank;            // P entries
+    uint32_t* order;            // P entries
+    int use_order;              // this launch walks `order` (set by the iteration for the launch that has one)
+    int key_obits, key_dbits;   // key = Morton code of the origin cell (obits per axis) << 3 * dbits | direction bin (dbits per axis)
+    float3 key_lo, key_scale;   // origin -> cell: (o - key_lo) * key_scale in [0, 2^obits)
     float4* accum;      // Nx*Ny linear radiance sums (rgb) + sample count (w)
     int P;
     int Nx, Ny;

@@ -133,7 +133,11 @@ RTW_HD bool closest_ray_of(const DScene& sc, const DWave& w, uint32_t slot, RayW
 }
 template <class Mem>
 RTW_HD int closest_result(const DScene& sc, const DWave& w, uint32_t slot, bool found, float t, uint32_t leaf) {
+#ifdef RTW_HIT_IN_RECORD   // experiment (profiles/r02/hit_in_record_r02f.md): the hit rides in the 8 spare bytes of the slot record
+    w.rec[slot].st.spare = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
+#else
     w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
+#endif
     if (!found) return RTW_Q_TERMINAL;
     const int mt = meta_mattype(f2u(Mem::ld4(sc.prims + 2 * leaf + 1).w));
     if (mt == RTW_MAT_LAMBERTIAN) return RTW_Q_LAMBERTIAN;
@@ -177,7 +181,9 @@ RTW_HD void prefetch_slot(const DWave& w, uint32_t ahead) {
 #if defined(__CUDA_ARCH__)
     if (ahead != RTW_REF_NONE) {
         asm volatile("prefetch.global.L2 [%0];" ::"l"(w.rec + ahead));
+#ifndef RTW_HIT_IN_RECORD
         asm volatile("prefetch.global.L2 [%0];" ::"l"(w.hit + ahead));
+#endif
     }
 #else
     (void)w; (void)ahead;
@@ -188,7 +194,11 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
     sh.emit = false;
     const RayRec ray = w.rec[slot].ray;
     const PathRec st = w.rec[slot].st;
+#ifdef RTW_HIT_IN_RECORD
+    const uint2 hit = st.spare;
+#else
     const uint2 hit = w.hit[slot];
+#endif
     prefetch_slot(w, ahead);
     const float4 ro = ray.o, rd = ray.d;
     const float4 th = st.thr;

@@ -10,11 +10,13 @@ namespace rtw {
 // ---- radix sort (kernels/sort.cu) -----------------------------------------
 // Stable LSD radix sort of (64-bit key, 32-bit value) pairs, 8 passes of 8 bits.
 // keys/vals are ping-pong buffers of n elements each; the sorted result ends in
-// keys[0]/vals[0].  scratch must hold sort_scratch_words(n) uint32 (digit histograms, tile tickets, the
-// look-back status words of the tiles); sort_pairs clears it itself.
+// keys[0]/vals[0].  scratch must hold sort_scratch_words(n) uint32 (digit totals per pass, per-tile digit counts);
+// sort_pairs clears what it needs itself.
 size_t sort_scratch_words(int n);
+// passes: the low `passes` 8-bit digits are sorted (8 = whole keys); after an odd number the result is in keys[1]/vals[1].
 cudaError_t sort_pairs(cudaStream_t s, unsigned long long* keys[2], uint32_t* vals[2], int n, uint32_t* scratch,
-                       uint64_t* launches);
+                       uint64_t* launches, int passes = 8);
+
 
 // ---- LBVH build (kernels/lbvh.cu) -------------------------------------------
 struct BuildBuffers {
@@ -61,6 +63,7 @@ struct LaunchCfg {
     int node_min, prim_min;                   // persistent traversal: warp-vote thresholds of the inner loops (0 = plain step)
     int shade_ctas;         // k_shade_all variant: resident CTAs per SM its registers are held to (2, 3 or 4)
     bool walker;            // persistent walker kernels (else the flat per-thread traversal kernels)
+    bool sort_shadow;       // option sort_rays >= 2: the NEE rays are binned too
     bool stream;            // streaming wavefront (kernels/stream.cu) instead of the slot pool (kernels/wavefront.cu)
     int grid_fill, grid_stream;   // its two grids
     cudaEvent_t mid_event;  // if set: recorded in the middle of the iteration (after the traversal / fill launch)

@@ -112,8 +112,11 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     static constexpr bool kAny = false;
     const DScene& sc;
     const DWave& w;
-    __device__ uint32_t count() const { return (uint32_t)w.P; }
+    // option sort_rays: only the slots that hold a ray are in `order`
+    __device__ uint32_t count() const { return w.use_order ? w.bins[1 << (3 * (w.key_obits + w.key_dbits))] : (uint32_t)w.P; }
     __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_CLOSEST; }
+    // work index -> slot: pool order, or bin by bin
+    __device__ uint32_t item_of(uint32_t i) const { return w.use_order ? __ldg(w.order + i) : i; }
     __device__ bool load(uint32_t slot, RayW& r) const {
         const RayRec ray = w.rec[slot].ray;
         const float4 ro = ray.o, rd = ray.d;
@@ -129,7 +132,11 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     }
     // returns the shading class of the finished slot
     __device__ int store(uint32_t slot, bool found, float t, uint32_t leaf) const {
+#ifdef RTW_HIT_IN_RECORD
+        w.rec[slot].st.spare = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
+#else
         w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
+#endif
         if (!found) return RTW_Q_TERMINAL;
         const int mt = meta_mattype(f2u(__ldg(sc.prims + 2 * leaf + 1).w));
         if (mt == RTW_MAT_LAMBERTIAN) return RTW_Q_LAMBERTIAN;
@@ -146,6 +153,7 @@ struct ShadowJob {       // stage 3: the NEE rays (closehit.cu:16-42,97-113): tm
     const DWave& w;
     __device__ uint32_t count() const { return w.counters[RTW_C_SHADOW]; }
     __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_SHADOW; }
+    __device__ uint32_t item_of(uint32_t i) const { return w.use_order ? __ldg(w.order + i) : i; }
     __device__ bool load(uint32_t i, RayW& r) const {
         const float4 so = w.sh_o[i];
         const float4 sd = w.sh_d[i];
@@ -179,6 +187,7 @@ struct TraceJob {        // test hook: caller-supplied rays (rtw_trace_closest /
     uint32_t* counter;
     __device__ uint32_t count() const { return (uint32_t)n; }
     __device__ uint32_t* work() const { return counter; }
+    __device__ uint32_t item_of(uint32_t i) const { return i; }
     __device__ bool load(uint32_t i, RayW& r) const {
         const rtw_ray a = rays[i];
         r.o = f3(a.origin[0], a.origin[1], a.origin[2]);
@@ -246,10 +255,11 @@ __device__ __forceinline__ void walk_persistent(const DScene& sc, const DWave* w
             const uint32_t idx = base + __popc(idle & lt);
             if (idx < total) {
                 RayW r;
-                if (job.load(idx, r)) {
+                const uint32_t it = job.item_of(idx);   // work index -> item (ClosestJob: the slot, in pool or sorted order)
+                if (job.load(it, r)) {
                     wk.begin(sc, r, stack);
                     active = true;
-                    item = idx;
+                    item = it;
                 }
             }
         }
@@ -366,6 +376,119 @@ __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const 
     }
     if ((threadIdx.x & 31u) == 0u && n_unocc) atomic_add_u64(w.counters + RTW_C_UNOCC_LO, (unsigned long long)n_unocc);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomic_add_u64(w.counters + RTW_C_SHRAYS_LO, (unsigned long long)n);
+}
+
+// ---- option sort_rays: counting sort of a stage's rays by (origin cell, direction bin) -----------------------------
+// Incoherent rays leave the lanes of a walker warp in different parts of the hierarchy (ncu, scene 4: 8.8 of 32 lanes
+// per instruction).  Rays that start in the same cell and head the same way walk the same nodes: the stage takes its
+// rays bin by bin.  Which ray a lane gets does not change the ray's result (closest hit = min (t, primitive id)).
+//   k_ray_bin    item -> key; rank inside the bin from ONE atomicAdd per warp and key (__match_any_sync)
+//   k_bin_sum, k_bin_scan   bins: counts -> first positions (<= 2^18 bins); bins[n_bins] = items placed
+//   k_ray_place  order[first[key] + rank] = item
+__device__ __forceinline__ uint32_t ray_key(const DWave& w, float3 o, float3 d) {
+    const float top = (float)((1 << w.key_obits) - 1);
+    const uint32_t ix = (uint32_t)fminf(fmaxf((o.x - w.key_lo.x) * w.key_scale.x, 0.f), top);
+    const uint32_t iy = (uint32_t)fminf(fmaxf((o.y - w.key_lo.y) * w.key_scale.y, 0.f), top);
+    const uint32_t iz = (uint32_t)fminf(fmaxf((o.z - w.key_lo.z) * w.key_scale.z, 0.f), top);
+    uint32_t m = 0;
+    for (int b = 0; b < w.key_obits; b++) m |= (((ix >> b) & 1u) << (3 * b + 2)) | (((iy >> b) & 1u) << (3 * b + 1)) | (((iz >> b) & 1u) << (3 * b));
+    const float dm = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fmaxf(fabsf(d.z), 1e-30f));
+    const float half = (float)(1 << (w.key_dbits - 1)), dtop = (float)((1 << w.key_dbits) - 1);
+    const uint32_t qx = (uint32_t)fminf(fmaxf((d.x / dm + 1.0f) * half, 0.f), dtop);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((d.y / dm + 1.0f) * half, 0.f), dtop);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((d.z / dm + 1.0f) * half, 0.f), dtop);
+    return (m << (3 * w.key_dbits)) | (qx << (2 * w.key_dbits)) | (qy << w.key_dbits) | qz;
+}
+template <bool kShadow>
+__global__ void __launch_bounds__(kBlock) k_ray_bin(const DWave w) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = kShadow ? w.counters[RTW_C_SHADOW] : (uint32_t)w.P;
+    if (i - lane >= n) return;   // whole warps only: the vote below needs every lane
+    uint32_t key = 0x80000000u | lane;   // no ray: a key of its own (matches no other lane), not binned
+    if (i < n) {
+        if (kShadow) {
+            key = ray_key(w, f3(w.sh_o[i]), f3(w.sh_d[i]));
+        } else {
+            const RayRec ray = w.rec[i].ray;
+            if (f2u(ray.o.w) != RTW_RAY_NONE) key = ray_key(w, f3(ray.o), f3(ray.d));
+        }
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, key);
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    const bool binned = !(key & 0x80000000u);
+    if (binned && (int)lane == leader) base = atomicAdd(w.bins + key, (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (i < n) w.bin_rank[i] = make_uint2(key, base + (uint32_t)__popc(peers & ((1u << lane) - 1u)));
+}
+// bins: counts -> first positions, in two launches of n_bins / 1024 CTAs (a one-CTA scan of 2^18 bins is a chain of
+// 512 dependent L2 accesses per thread: 0.5 ms).  part[] = the sums of the 1024-bin chunks, behind bins[n_bins].
+__device__ __forceinline__ uint32_t block_scan_1024(uint32_t v, uint32_t* s_warp, uint32_t& total) {   // exclusive
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t before = 0, all = 0;
+#pragma unroll
+    for (int k = 0; k < 32; k++) {
+        const uint32_t x = s_warp[k];
+        before += k < warp ? x : 0u;
+        all += x;
+    }
+    total = all;
+    return before + inc - v;
+}
+__global__ void __launch_bounds__(1024) k_bin_sum(const DWave w) {
+    __shared__ uint32_t s_warp[32];
+    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    const int k = blockIdx.x * 1024 + threadIdx.x;
+    uint32_t total;
+    block_scan_1024(k < n_bins ? w.bins[k] : 0u, s_warp, total);
+    if (threadIdx.x == 0) w.bins[n_bins + 1 + blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(1024) k_bin_scan(const DWave w) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_warp2[32];
+    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    const uint32_t* part = w.bins + n_bins + 1;
+    uint32_t mine = 0;   // chunks in front of this one (at most 256)
+    for (int j = threadIdx.x; j < (int)blockIdx.x; j += 1024) mine += part[j];
+    uint32_t base;
+    block_scan_1024(mine, s_warp2, base);
+    const int k = blockIdx.x * 1024 + threadIdx.x;
+    const uint32_t c = k < n_bins ? w.bins[k] : 0u;
+    uint32_t total;
+    const uint32_t excl = block_scan_1024(c, s_warp, total);
+    if (k < n_bins) w.bins[k] = base + excl;
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) w.bins[n_bins] = base + total;   // items placed
+}
+template <bool kShadow>
+__global__ void __launch_bounds__(kBlock) k_ray_place(const DWave w) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = kShadow ? w.counters[RTW_C_SHADOW] : (uint32_t)w.P;
+    if (i >= n) return;
+    const uint2 kr = w.bin_rank[i];
+    if (!(kr.x & 0x80000000u)) w.order[w.bins[kr.x] + kr.y] = i;
+}
+// One counting sort on stream s (a memset of the bins + 4 launches).
+template <bool kShadow>
+cudaError_t bin_rays(cudaStream_t s, const DWave& w, uint64_t* launches) {
+    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    cudaError_t e = cudaMemsetAsync(w.bins, 0, sizeof(uint32_t) * (size_t)(n_bins + 1), s);
+    if (e != cudaSuccess) return e;
+    const int grid = (w.P + kBlock - 1) / kBlock;
+    k_ray_bin<kShadow><<<grid, kBlock, 0, s>>>(w);
+    k_bin_sum<<<(n_bins + 1023) / 1024, 1024, 0, s>>>(w);
+    k_bin_scan<<<(n_bins + 1023) / 1024, 1024, 0, s>>>(w);
+    k_ray_place<kShadow><<<grid, kBlock, 0, s>>>(w);
+    if (launches) *launches += 4;
+    return cudaGetLastError();
 }
 
 // resident CTAs per SM the persistent walkers' registers are held to: 4 -> 64 registers, 24-90 bytes of spills.
@@ -715,7 +838,17 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (ev) cudaEventRecord(ev[1], s);
     if (cfg.small) k_traverse_small<<<cfg.grid_traverse, kBlock, 0, s>>>(sc, w, *cfg.small);
     else if (!cfg.walker) k_traverse_flat<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w);
-    else k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
+    else {
+        DWave wt = w;
+        wt.use_order = 0;
+        if (w.bins) {   // option sort_rays: the walkers take the rays bin by bin
+            const cudaError_t e = bin_rays<false>(s, w, &l);
+            if (e != cudaSuccess) return e;
+            wt.use_order = 1;
+            if (ev) cudaEventRecord(ev[1], s);   // the binning is booked on the regeneration stage: `traverse` stays the walk itself
+        }
+        k_traverse<<<cfg.grid_traverse, kBlock, cfg.smem_top, s>>>(sc, wt, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
+    }
     l++;
     if (cfg.mid_event) cudaEventRecord(cfg.mid_event, s);
     if (ev) cudaEventRecord(ev[2], s);
@@ -733,7 +866,17 @@ cudaError_t wavefront_iteration(cudaStream_t s, const DScene& sc, const DWave& w
     if (cfg.has_shadow && !fused) {
         if (cfg.small) k_shadow_small<<<cfg.grid_shadow, kBlock, 0, s>>>(sc, w, *cfg.small);
         else if (!cfg.walker) k_shadow_flat<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w);
-        else k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, w, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
+        else {
+            DWave wt = w;
+            wt.use_order = 0;
+            if (w.bins && cfg.sort_shadow) {   // the NEE rays too (the queue is in the order the shading warps finished)
+                const cudaError_t e = bin_rays<true>(s, w, &l);
+                if (e != cudaSuccess) return e;
+                wt.use_order = 1;
+                if (ev) cudaEventRecord(ev[3], s);   // booked on the shading stage
+            }
+            k_shadow<<<cfg.grid_shadow, kBlock, cfg.smem_top, s>>>(sc, wt, WalkCfg{cfg.step_nodes, cfg.step_prims, cfg.min_active, cfg.node_min, cfg.prim_min});
+        }
         l++;
     }
     if (ev) cudaEventRecord(ev[4], s);

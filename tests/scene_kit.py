@@ -87,6 +87,9 @@ class KitScene:
         self.sky = 0
         self._keep = []
 
+    def close(self):
+        """Nothing to free (plain ctypes arrays); Director.destroy() calls it on whatever scene it holds."""
+
     # ---- textures / materials ----
     def tex(self, type, color=(0, 0, 0), odd=-1, even=-1, scale=0.0, perlin=-1, image=-1):
         t = self.rtw.Texture()

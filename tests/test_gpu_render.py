@@ -316,7 +316,11 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
                      {"walker": 1, "step_nodes": 64, "step_prims": 32, "min_active": 1},
                      {"walker": 1, "step_nodes": 16, "step_prims": 8, "min_active": 22, "node_min": 8, "prim_min": 4},
                      {"walker": 1, "step_nodes": 5, "step_prims": 3, "min_active": 30, "node_min": 32, "prim_min": 32},
-                     {"walker": 1, "step_nodes": 16, "step_prims": 8, "min_active": 12, "node_min": 1, "prim_min": 0}):
+                     {"walker": 1, "step_nodes": 16, "step_prims": 8, "min_active": 12, "node_min": 1, "prim_min": 0},
+                     # the walkers take the rays in (origin cell, direction bin) order instead of slot order
+                     {"walker": 1, "stream": 0, "small": 0, "step_nodes": 8, "node_min": 0, "prim_min": 0, "min_active": 22, "sort_rays": 1},
+                     {"walker": 1, "sort_rays": 2, "sort_obits": 3, "sort_dbits": 2}, {"walker": 1, "sort_rays": 2, "sort_obits": 5, "sort_dbits": 1},
+                     {"walker": 1, "sort_rays": 0}):
             for k, v in opts.items():
                 director.set_option(k, v)
             director.createScene(sid)
@@ -331,6 +335,6 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             rh, _ = o.trace_closest(director.camera_rays(0), 1)
             assert np.array_equal(hits, rh)
     finally:
-        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 16, "step_prims": 8, "min_active": 22,
-                     "tail_paths": 131072, "node_min": 0, "prim_min": 0}.items():
+        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 8, "step_prims": 8, "min_active": 22,
+                     "tail_paths": 131072, "node_min": 0, "prim_min": 0, "sort_rays": -1, "sort_obits": 5, "sort_dbits": 1}.items():
             director.set_option(k, v)
