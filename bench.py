@@ -440,8 +440,8 @@ def main():
                 "config": {"workload": WORKLOAD if spp == SPP else WORKLOAD.replace("1024 spp", "%d spp (override)" % spp),
                            "parallelism": "sample-sharded x%d, one NCCL reduce per frame; on each GPU the samples are dealt to "
                                           "%d concurrent pools (waves) on separate streams" % (world, waves),
-                           "l2_policy": "inputs larger than L2: the wavefront pools (%d x %d path slots per GPU x 160 B state + queues = %d MB) "
-                                        "stream through HBM every iteration, no flush between steps" % (waves, pool, waves * pool * 160 >> 20),
+                           "l2_policy": "inputs larger than L2: the wavefront pools (%d x %d path slots per GPU x 156 B state + queues = %d MB) "
+                                        "stream through HBM every iteration, no flush between steps" % (waves, pool, waves * pool * 156 >> 20),
                            "wall_ms_per_step": wall / args.steps * 1e3,
                            "frame_phases_ms_rank0": {k: v / args.steps for k, v in trace.items()}},
                 "mrays_per_s": (tot[0].item() + tot[1].item()) / (dev_ms * 1e-3) / 1e6,
@@ -449,7 +449,7 @@ def main():
                 "gpu_launches": int(tot[2].item()), "clocks": clk.summary()}
         # ---- roofline: algorithmic bytes per unit x units / live kernel time ----
         # HBM-visible ALGORITHMIC bytes: closest-hit ray = the 32-byte ray record read + hit 8 + queue
-        # entry 4 written = 44 B; shaded vertex = queue entry 4 + slot record 64 + hit 8 read, then 64 written by a path
+        # entry 4 written = 44 B; shaded vertex = queue entry 4 + slot record 64 (the hit rides in it) read, then 64 written by a path
         # that continues or radiance record (16 R + 16 W) + regen entry 4 by one that ends, + 48 per NEE ray emitted;
         # shadow ray = 48 read + 32 per contribution added; finished path = 116.  Streaming wavefront (LBVH scenes
         # without NEE): a vertex = one 80-byte entry read + one written.  The BVH nodes / primitive records of §8d
@@ -468,7 +468,7 @@ def main():
                      ("k_stream_shade", agg["shade_ms"], rays_c, 160.0),
                      ("k_stream_advance", agg["shadow_ms"], iters, 128.0))
         else:
-            shade_bpu = 76.0 + 64.0 * (1.0 - fin) + 36.0 * fin + 48.0 * rays_s / rays_c
+            shade_bpu = 68.0 + 64.0 * (1.0 - fin) + 36.0 * fin + 48.0 * rays_s / rays_c
             table = (("k_traverse", agg["trav_ms"], rays_c, 44.0),
                      ("k_shade*", agg["shade_ms"], rays_c, shade_bpu),
                      ("k_shadow", agg["shadow_ms"], rays_s, 48.0 + 32.0 * unocc),

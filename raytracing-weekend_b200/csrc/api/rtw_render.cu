@@ -47,7 +47,6 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
         RTW_CUDA(c, dalloc(pool, &w.sq, (size_t)2 * 4 * 5 * P));
     } else {
         RTW_CUDA(c, dalloc(pool, &w.rec, P));
-        RTW_CUDA(c, dalloc(pool, &w.hit, P));
         RTW_CUDA(c, dalloc(pool, &w.rad, P));
         RTW_CUDA(c, dalloc(pool, &w.queue, (size_t)RTW_Q_SLOTS * P));
         RTW_CUDA(c, dalloc(pool, &w.sh_o, P));

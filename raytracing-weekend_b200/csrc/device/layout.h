@@ -151,7 +151,7 @@ struct SmallScene {
 };
 
 // ---- wavefront state: structure of arrays over P path slots ---------------
-// bytes per slot: ray 32 + hit 8 + throughput/seed 16 + radiance/pixel 16 + misc 8 = 80
+// bytes per slot: ray 32 + throughput/seed 16 + misc 8 + hit 8 (one 64-byte record) + radiance/pixel 16 = 80
 #define RTW_ST_EMPTY 0u
 #define RTW_ST_ALIVE 1u
 #define RTW_ST_DEAD  2u     // finished: radiance waits to be flushed by k_logic
@@ -198,7 +198,7 @@ struct __align__(32) RayRec {
 struct __align__(32) PathRec {
     float4 thr;         // throughput.xyz, path seed bits
     uint2 misc;         // (depth | state << 8, ray-time seed)
-    uint2 spare;        // written as zero so that a store covers the whole sector
+    uint2 hit;          // (t bits, leaf index or RTW_REF_NONE) of the slot's current ray: written by the closest-hit stage, read by shading
 };
 struct __align__(64) SlotRec {   // one 64-byte line per slot: L2 fetches DRAM in 64-byte pairs of sectors (the
     RayRec ray;                  // default cudaLimitMaxL2FetchGranularity), so a shading warp that gathers ray +
@@ -209,7 +209,6 @@ struct __align__(64) SlotRec {   // one 64-byte line per slot: L2 fetches DRAM i
 
 struct DWave {
     SlotRec* rec;       // current ray + path state of the slot
-    uint2*  hit;        // (t bits, leaf index or RTW_REF_NONE): written by the traversal in slot order
     float4* rad;        // radiance sum .xyz, pixel index bits (touched only when light is added)
     uint32_t* queue;    // RTW_Q_SLOTS * P slot indices
     float4* sh_o;       // shadow queue: origin.xyz, tmax

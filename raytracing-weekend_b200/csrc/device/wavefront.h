@@ -48,7 +48,7 @@ RTW_HD void retire_slot(const DWave& w, uint32_t slot) {
     PathRec st;
     st.thr = make_float4(0.f, 0.f, 0.f, 0.f);
     st.misc = make_uint2(misc_pack(0, RTW_ST_EMPTY), 0u);
-    st.spare = make_uint2(0u, 0u);
+    st.hit = make_uint2(0u, 0u);
     w.rec[slot].st = st;
     w.rad[slot] = make_float4(0.f, 0.f, 0.f, u2f(RTW_PIXEL_NONE));
 }
@@ -83,7 +83,7 @@ RTW_HD NewPath make_path(const DScene& sc, const DWave& w, unsigned long long or
     np.ray.o = make_float4(origin.x, origin.y, origin.z, ray_time);
     np.ray.d = make_float4(direction.x, direction.y, direction.z, gather);
     np.st.thr = make_float4(1.0f, 1.0f, 1.0f, u2f(s4));
-    np.st.spare = make_uint2(0u, 0u);
+    np.st.hit = make_uint2(0u, 0u);
     np.rad = make_float4(0.f, 0.f, 0.f, u2f(pixel));
     // `while (depth < maxRayDepth)` (raygen.cu:36): with a depth limit of 0 no ray is traced
     np.st.misc = make_uint2(misc_pack(0, w.max_depth > 0 ? RTW_ST_ALIVE : RTW_ST_DEAD), lseed);
@@ -133,11 +133,9 @@ RTW_HD bool closest_ray_of(const DScene& sc, const DWave& w, uint32_t slot, RayW
 }
 template <class Mem>
 RTW_HD int closest_result(const DScene& sc, const DWave& w, uint32_t slot, bool found, float t, uint32_t leaf) {
-#ifdef RTW_HIT_IN_RECORD   // experiment (profiles/r02/hit_in_record_r02f.md): the hit rides in the 8 spare bytes of the slot record
-    w.rec[slot].st.spare = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
-#else
-    w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
-#endif
+    // the hit rides in the last 8 bytes of the slot record: the shading gather then touches ONE 64-byte line per slot
+    // (profiles/r02/hit_in_record_r02g.md: k_shade_all 396 -> 344 MB of DRAM traffic per launch, C2 +1.8 %)
+    w.rec[slot].st.hit = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
     if (!found) return RTW_Q_TERMINAL;
     const int mt = meta_mattype(f2u(Mem::ld4(sc.prims + 2 * leaf + 1).w));
     if (mt == RTW_MAT_LAMBERTIAN) return RTW_Q_LAMBERTIAN;
@@ -181,9 +179,6 @@ RTW_HD void prefetch_slot(const DWave& w, uint32_t ahead) {
 #if defined(__CUDA_ARCH__)
     if (ahead != RTW_REF_NONE) {
         asm volatile("prefetch.global.L2 [%0];" ::"l"(w.rec + ahead));
-#ifndef RTW_HIT_IN_RECORD
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(w.hit + ahead));
-#endif
     }
 #else
     (void)w; (void)ahead;
@@ -194,11 +189,7 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
     sh.emit = false;
     const RayRec ray = w.rec[slot].ray;
     const PathRec st = w.rec[slot].st;
-#ifdef RTW_HIT_IN_RECORD
-    const uint2 hit = st.spare;
-#else
-    const uint2 hit = w.hit[slot];
-#endif
+    const uint2 hit = st.hit;
     prefetch_slot(w, ahead);
     const float4 ro = ray.o, rd = ray.d;
     const float4 th = st.thr;
@@ -306,7 +297,7 @@ RTW_HD bool shade_thread(const DScene& sc, const DWave& w, uint32_t slot, Shadow
         PathRec ns;
         ns.thr = make_float4(throughput.x, throughput.y, throughput.z, u2f(seed));
         ns.misc = make_uint2(misc_pack(depth, state), lseed);
-        ns.spare = make_uint2(0u, 0u);
+        ns.hit = make_uint2(0u, 0u);
         w.rec[slot].st = ns;
     }
     if (touch_rad) {

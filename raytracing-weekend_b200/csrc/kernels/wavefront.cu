@@ -132,11 +132,7 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     }
     // returns the shading class of the finished slot
     __device__ int store(uint32_t slot, bool found, float t, uint32_t leaf) const {
-#ifdef RTW_HIT_IN_RECORD
-        w.rec[slot].st.spare = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
-#else
-        w.hit[slot] = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
-#endif
+        w.rec[slot].st.hit = make_uint2(f2u(t), found ? leaf : RTW_REF_NONE);
         if (!found) return RTW_Q_TERMINAL;
         const int mt = meta_mattype(f2u(__ldg(sc.prims + 2 * leaf + 1).w));
         if (mt == RTW_MAT_LAMBERTIAN) return RTW_Q_LAMBERTIAN;

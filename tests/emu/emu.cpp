@@ -305,10 +305,9 @@ extern "C" int emu_render(const Emu* e, int Nx, int Ny, int sample_first, int sa
     const DScene& sc = e->sc;
     std::vector<SlotRec> rec(P);
     std::vector<float4> rad(P), sh_o(P), sh_d(P), sh_c(P);
-    std::vector<uint2> hit(P);
     std::vector<uint32_t> queue((size_t)RTW_Q_SLOTS * P), counters(RTW_C_WORDS, 0);
     DWave w{};
-    w.rec = rec.data(); w.hit = hit.data(); w.rad = rad.data();
+    w.rec = rec.data(); w.rad = rad.data();
     w.queue = queue.data(); w.sh_o = sh_o.data(); w.sh_d = sh_d.data(); w.sh_c = sh_c.data();
     w.counters = counters.data(); w.accum = reinterpret_cast<float4*>(accum);
     w.P = P; w.Nx = Nx; w.Ny = Ny; w.max_depth = max_depth;
