@@ -151,6 +151,8 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "sort_rays")) {
         if (value < -1 || value > 2) return fail(c, RTW_ERR_INVALID, "sort_rays out of range [-1, 2]");
         c->opt_sort_rays = (int)value;
+    } else if (!strcmp(name, "sort_camera")) {
+        c->opt_sort_camera = value != 0;
     } else if (!strcmp(name, "sort_obits") || !strcmp(name, "sort_dbits")) {
         if (value < 1 || value > 5) return fail(c, RTW_ERR_INVALID, "sort_obits / sort_dbits out of range [1, 5]");
         if (name[5] == 'o') c->opt_sort_obits = (int)value;
@@ -425,11 +427,16 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     if (n <= b.leaf_size) sc.root = leaf_range_ref(0, n);
     else sc.root = sc.n_top > 0 ? (RTW_REF_TOP | 0u) : 0u;
     c->n_internal = ni_tree;
-    // Traversal variant (tools/sweep_walk.sh, B200, 64 spp): persistent walkers win on the deep
-    // hierarchy of the Book-2 scene (3410 primitives: k_traverse 0.77 -> 0.60 ms per 2 M rays) but
-    // lose ~10 % on the 520-528 primitive scenes, where rays finish within a few steps of each other and
-    // the finish-order queue pushes cost the shading kernels their slot-order coalescing.
-    c->cfg.walker = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 1024);
+    // Traversal variant.  Persistent walkers (dynamic ray fetching) win on deep hierarchies (round 1, tools/sweep_walk.sh:
+    // Book-2 final scene, 3410 primitives, k_traverse 0.77 -> 0.60 ms per 2 M rays); on the 520-528 primitive scenes
+    // they lost ~10 % to the flat kernels until the rays were taken bin by bin (round 2, option sort_rays,
+    // profiles/r02/sort_rays_r02f.md): with the binning the walkers also win on the Book-2 spheres scene (520 primitives,
+    // NEE: 975 against 901 Mpaths/s), while the Book-1 scene (528 primitives, no NEE) stays with the streaming
+    // wavefront (1635 against 1353); on the sky-lit stress scenes streaming leads up to 2^14 primitives (3244 against
+    // 3029 at 2048, 1524 against 1507 at 16 384) and falls behind above (491 against 592 at 2^17, 136 against 260 at 2^20).
+    // Auto: walkers above 16 384 primitives, and for every LBVH scene with an NEE stage.
+    const bool nee_stage = sc.n_lights > 0 && sc.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN));
+    c->cfg.walker = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 16384 || (nee_stage && n > RTW_SMALL_MAX));
     // Small scenes (one leaf range, <= RTW_SMALL_MAX leaves and transforms): the leaf records go to
     // the traversal kernels by value.
     c->cfg.small = nullptr;

@@ -37,7 +37,7 @@ struct rtw_ctx {
         std::vector<void*> allocs;
         rtw::DWave w{};
         int capacity = 0;
-        int key_bits = 0;                   // option sort_rays: the bins were allocated for 2^key_bits keys
+        int key_bits = 0;                   // option sort_rays: the number of bins the arrays were allocated for
         bool for_stream = false;            // what the pool was allocated for (streaming wavefront or slot pool)
         cudaStream_t stream = nullptr;
         uint32_t* h_counters = nullptr;     // pinned ring of counter snapshots
@@ -75,11 +75,12 @@ struct rtw_ctx {
     int opt_fuse_shadow = 0;         // 1 = by-value small scenes trace their NEE rays inside k_shade_all (no shadow queue, no k_shadow_small launch).
                                      // Measured on the B200, C2 (profiles/r02/r02c_fuse_shadow.md): 2656 Mpaths/s fused against 3057 with the queue —
                                      // the separate shadow launch is what the OTHER wave's DRAM-bound shading launch overlaps with; default off
-    // LBVH walkers take their rays bin by bin, bin = (origin cell, direction bin): 1 = closest-hit rays, 2 = NEE rays too,
-    // 0 = off, -1 = auto: 1 for walker scenes with an NEE stage (closed scenes, long diffuse paths: most rays of an iteration
-    // are incoherent bounce rays).  Measured (profiles/r02/sort_rays_r02f.md): scene 4 468 -> 533 Mpaths/s; nothing on the
-    // sky-lit stress scenes (2^14..2^20 primitives: camera rays and short paths), negative where the flat kernels win.
+    // LBVH walkers take their rays bin by bin — camera rays by direction (cube map), bounce rays by (origin cell, direction
+    // octant): 1 = closest-hit rays, 2 = NEE rays too, 0 = slot order, -1 = auto: 1 on every walker scene.  Measured
+    // (profiles/r02/sort_rays_r02f.md): scene 4 468 -> 592 Mpaths/s, scene 2 901 -> 975 (walkers instead of the flat kernels),
+    // stress scenes of 2^14 / 2^17 / 2^20 primitives 1285 -> 1515, 528 -> 594, 229 -> 260.
     int opt_sort_rays = -1;
+    int opt_sort_camera = 1;         // camera rays get direction bins of their own (6 x 256 x 256 on a cube map)
     int opt_sort_obits = 5, opt_sort_dbits = 1;   // bits per axis of the origin cell / of the direction bin (obits + dbits <= 6: 2^18 bins)
     float key_lo[3] = {0, 0, 0}, key_hi[3] = {0, 0, 0};   // bounds of the primitive centroids (rtw_build_accel): the cells of the ray keys
     int opt_profile = 0;

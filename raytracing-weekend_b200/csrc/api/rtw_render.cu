@@ -19,20 +19,23 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
         for (auto& e : wv.ev_iter) RTW_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         RTW_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&wv.h_counters), sizeof(uint32_t) * RTW_C_WORDS * 8));
     }
-    const int sort_rays = c->opt_sort_rays >= 0 ? c->opt_sort_rays : (c->cfg.has_shadow ? 1 : 0);   // -1 = auto (rtw_ctx.h)
-    const bool want_sort = sort_rays > 0 && !stream && c->cfg.walker && !c->cfg.small;
+    const int sort_rays = c->opt_sort_rays >= 0 ? c->opt_sort_rays : 1;   // -1 = auto (rtw_ctx.h): every walker scene
+    const bool want_sort = sort_rays > 0 && !stream && c->cfg.walker && !c->cfg.small && !(c->scene.root & RTW_REF_LEAF);
     const int key_ob = c->opt_sort_obits, key_db = std::max(1, std::min(c->opt_sort_dbits, 6 - key_ob));   // at most 2^18 bins
     const int key_bits = 3 * (key_ob + key_db);
+    const int n_bins = (1 << key_bits) + (c->opt_sort_camera ? RTW_CAMERA_BINS : 0);   // + the camera rays' direction bins (kernels/wavefront.cu)
     auto set_key_cells = [&](DWave& w) {   // the ray keys' origin cells span the bounds of the primitive centroids
         w.key_obits = key_ob;
         w.key_dbits = key_db;
+        w.key_camera = c->opt_sort_camera;
+        w.n_bins = n_bins;
         for (int k = 0; k < 3; k++) {
             const float ext = c->key_hi[k] - c->key_lo[k];
             (&w.key_lo.x)[k] = c->key_lo[k];
             (&w.key_scale.x)[k] = ext > 0.f ? (float)(1 << c->opt_sort_obits) / ext : 0.f;
         }
     };
-    if (wv.capacity >= P && wv.for_stream == stream && (wv.w.bins != nullptr) == want_sort && (!want_sort || wv.key_bits == key_bits)) {
+    if (wv.capacity >= P && wv.for_stream == stream && (wv.w.bins != nullptr) == want_sort && (!want_sort || wv.key_bits == n_bins)) {
         wv.w.P = P;
         set_key_cells(wv.w);
         return RTW_OK;
@@ -55,10 +58,10 @@ static int ensure_wave(rtw_ctx* c, int j, int P) {
     }
     RTW_CUDA(c, dalloc(pool, &w.counters, RTW_C_WORDS));
     if (want_sort) {
-        RTW_CUDA(c, dalloc(pool, &w.bins, ((size_t)1 << key_bits) + 1 + 256));   // counts / first positions, the total, the chunk sums
+        RTW_CUDA(c, dalloc(pool, &w.bins, (size_t)n_bins + 1 + (size_t)(n_bins + 1023) / 1024));   // counts / first positions, the total, the chunk sums
         RTW_CUDA(c, dalloc(pool, &w.bin_rank, P));
         RTW_CUDA(c, dalloc(pool, &w.order, P));
-        wv.key_bits = key_bits;
+        wv.key_bits = n_bins;
     }
     set_key_cells(w);
     w.P = P;

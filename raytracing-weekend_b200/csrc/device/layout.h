@@ -204,6 +204,7 @@ struct __align__(64) SlotRec {   // one 64-byte line per slot: L2 fetches DRAM i
     RayRec ray;                  // default cudaLimitMaxL2FetchGranularity), so a shading warp that gathers ray +
     PathRec st;                  // path state through queue indices pays for exactly the bytes it uses
 };
+#define RTW_CAMERA_BINS (6 * 65536)   // option sort_rays: direction bins of the camera rays (cube map, 256 x 256 per face)
 #define RTW_RAY_NONE   0xffffffffu   // RayRec.o.w of a slot without a live ray (a ray time is a number in [0, 1))
 #define RTW_PIXEL_NONE 0xffffffffu   // rad.w of a slot that holds nothing to flush
 
@@ -220,7 +221,9 @@ struct DWave {
     // of in slot / queue order.  One counting sort per stage and iteration (kernels/wavefront.cu k_ray_bin, k_bin_scan,
     // k_ray_place): bins[key] counts, then holds the first position of the bin; bin_rank[i] = (key, rank inside the bin)
     // of item i; order[position] = item.  bins[n_bins] = number of items placed (empty slots are left out).
-    uint32_t* bins;             // n_bins + 1 + 256 words (the last 256: sums of 1024-bin chunks); nullptr = option off
+    uint32_t* bins;             // n_bins + 1 + ceil(n_bins / 1024) words (counts / first positions, the total, sums of 1024-bin chunks); nullptr = option off
+    int n_bins;                 // 2^(3 * (key_obits + key_dbits)) regular bins + (key_camera ? the camera rays' direction bins : 0)
+    int key_camera;             // camera rays (depth 0) are binned by direction alone, in bins of their own (kernels/wavefront.cu camera_key)
     uint2* bin_rank;            // P entries
     uint32_t* order;            // P entries
     int use_order;              // this launch walks `order` (set by the iteration for the launch that has one)

@@ -113,7 +113,7 @@ struct ClosestJob {      // stage 1: every live slot of the pool (raygen.cu:41-5
     const DScene& sc;
     const DWave& w;
     // option sort_rays: only the slots that hold a ray are in `order`
-    __device__ uint32_t count() const { return w.use_order ? w.bins[1 << (3 * (w.key_obits + w.key_dbits))] : (uint32_t)w.P; }
+    __device__ uint32_t count() const { return w.use_order ? w.bins[w.n_bins] : (uint32_t)w.P; }
     __device__ uint32_t* work() const { return w.counters + RTW_C_WORK_CLOSEST; }
     // work index -> slot: pool order, or bin by bin
     __device__ uint32_t item_of(uint32_t i) const { return w.use_order ? __ldg(w.order + i) : i; }
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow_small(const DScene sc, const 
 // per instruction).  Rays that start in the same cell and head the same way walk the same nodes: the stage takes its
 // rays bin by bin.  Which ray a lane gets does not change the ray's result (closest hit = min (t, primitive id)).
 //   k_ray_bin    item -> key; rank inside the bin from ONE atomicAdd per warp and key (__match_any_sync)
-//   k_bin_sum, k_bin_scan   bins: counts -> first positions (<= 2^18 bins); bins[n_bins] = items placed
+//   k_bin_sum, k_bin_scan   bins: counts -> first positions; bins[n_bins] = items placed
 //   k_ray_place  order[first[key] + rank] = item
 __device__ __forceinline__ uint32_t ray_key(const DWave& w, float3 o, float3 d) {
     const float top = (float)((1 << w.key_obits) - 1);
@@ -395,6 +395,21 @@ __device__ __forceinline__ uint32_t ray_key(const DWave& w, float3 o, float3 d) 
     const uint32_t qz = (uint32_t)fminf(fmaxf((d.z / dm + 1.0f) * half, 0.f), dtop);
     return (m << (3 * w.key_dbits)) | (qx << (2 * w.key_dbits)) | (qy << w.key_dbits) | qz;
 }
+// Camera rays (depth 0) all leave one point: their cell says nothing and an octant holds the whole image, so they get
+// bins of their own behind the regular ones, by DIRECTION on a cube map — face, then 256 x 256 cells per face.
+// Neighbouring pixels then sit in the same or the next bin whatever slots their paths were started in.
+__device__ __forceinline__ uint32_t camera_key(float3 d) {
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    uint32_t face;
+    float m, u, v;
+    if (ax >= ay && ax >= az) { face = d.x < 0.f ? 1u : 0u; m = ax; u = d.y; v = d.z; }
+    else if (ay >= az) { face = d.y < 0.f ? 3u : 2u; m = ay; u = d.x; v = d.z; }
+    else { face = d.z < 0.f ? 5u : 4u; m = az; u = d.x; v = d.y; }
+    m = fmaxf(m, 1e-30f);
+    const uint32_t iu = (uint32_t)fminf(fmaxf((u / m + 1.0f) * 128.0f, 0.f), 255.f);
+    const uint32_t iv = (uint32_t)fminf(fmaxf((v / m + 1.0f) * 128.0f, 0.f), 255.f);
+    return (face << 16) | (iu << 8) | iv;
+}
 template <bool kShadow>
 __global__ void __launch_bounds__(kBlock) k_ray_bin(const DWave w) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -407,7 +422,10 @@ __global__ void __launch_bounds__(kBlock) k_ray_bin(const DWave w) {
             key = ray_key(w, f3(w.sh_o[i]), f3(w.sh_d[i]));
         } else {
             const RayRec ray = w.rec[i].ray;
-            if (f2u(ray.o.w) != RTW_RAY_NONE) key = ray_key(w, f3(ray.o), f3(ray.d));
+            if (f2u(ray.o.w) != RTW_RAY_NONE) {
+                const bool primary = w.key_camera && misc_depth(w.rec[i].st.misc.x) == 0u;   // (the same 64-byte line)
+                key = primary ? (1u << (3 * (w.key_obits + w.key_dbits))) + camera_key(f3(ray.d)) : ray_key(w, f3(ray.o), f3(ray.d));
+            }
         }
     }
     const uint32_t peers = __match_any_sync(0xffffffffu, key);
@@ -442,7 +460,7 @@ __device__ __forceinline__ uint32_t block_scan_1024(uint32_t v, uint32_t* s_warp
 }
 __global__ void __launch_bounds__(1024) k_bin_sum(const DWave w) {
     __shared__ uint32_t s_warp[32];
-    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    const int n_bins = w.n_bins;
     const int k = blockIdx.x * 1024 + threadIdx.x;
     uint32_t total;
     block_scan_1024(k < n_bins ? w.bins[k] : 0u, s_warp, total);
@@ -451,7 +469,7 @@ __global__ void __launch_bounds__(1024) k_bin_sum(const DWave w) {
 __global__ void __launch_bounds__(1024) k_bin_scan(const DWave w) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_warp2[32];
-    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    const int n_bins = w.n_bins;
     const uint32_t* part = w.bins + n_bins + 1;
     uint32_t mine = 0;   // chunks in front of this one (at most 256)
     for (int j = threadIdx.x; j < (int)blockIdx.x; j += 1024) mine += part[j];
@@ -475,7 +493,7 @@ __global__ void __launch_bounds__(kBlock) k_ray_place(const DWave w) {
 // One counting sort on stream s (a memset of the bins + 4 launches).
 template <bool kShadow>
 cudaError_t bin_rays(cudaStream_t s, const DWave& w, uint64_t* launches) {
-    const int n_bins = 1 << (3 * (w.key_obits + w.key_dbits));
+    const int n_bins = w.n_bins;
     cudaError_t e = cudaMemsetAsync(w.bins, 0, sizeof(uint32_t) * (size_t)(n_bins + 1), s);
     if (e != cudaSuccess) return e;
     const int grid = (w.P + kBlock - 1) / kBlock;
