@@ -386,7 +386,14 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // leaf ranges: a scene of <= 16 primitives is ONE range (every lane of a warp walks the
     // same primitive list: no traversal divergence at all); larger scenes collapse subtrees
     // of <= 4 primitives, which trades a few extra primitive tests for fewer node visits.
-    b.leaf_size = c->opt_leaf_size > 0 ? c->opt_leaf_size : (n <= 16 ? 16 : 4);
+    // (the walker rule explained at the traversal-variant block below; decided here because the leaf size follows it)
+    const bool nee_stage_pre = c->scene.n_lights > 0 && c->scene.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN));
+    const bool walker_pre = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 16384 || (nee_stage_pre && n > RTW_SMALL_MAX));
+    // Walker scenes: plain LBVH leaves.  With the rays arriving bin by bin the node visits run at good lane counts and the
+    // primitive tests of a range (mixed kinds, some lanes with 1 and some with 4 primitives) are what diverges: leaf
+    // size 1 against 4 is +8 % on scene 4, +30 % / +45 % on the stress scenes of 2^20 / 2^17 primitives
+    // (profiles/r02/lbvh_r02.md, tools/sweep_walk{3,4,5}.sh).  The flat / streaming kernels keep 4.
+    b.leaf_size = c->opt_leaf_size > 0 ? c->opt_leaf_size : (n <= 16 ? 16 : (walker_pre ? 1 : 4));
     c->leaf_size = b.leaf_size;
     const bool wide = c->opt_wide != 0 && n > b.leaf_size;
     b.wide = wide ? c->wide_nodes : nullptr;
@@ -435,8 +442,7 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // wavefront (1635 against 1353); on the sky-lit stress scenes streaming leads up to 2^14 primitives (3244 against
     // 3029 at 2048, 1524 against 1507 at 16 384) and falls behind above (491 against 592 at 2^17, 136 against 260 at 2^20).
     // Auto: walkers above 16 384 primitives, and for every LBVH scene with an NEE stage.
-    const bool nee_stage = sc.n_lights > 0 && sc.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN));
-    c->cfg.walker = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 16384 || (nee_stage && n > RTW_SMALL_MAX));
+    c->cfg.walker = walker_pre;   // (decided before the build: the leaf size follows it)
     // Small scenes (one leaf range, <= RTW_SMALL_MAX leaves and transforms): the leaf records go to
     // the traversal kernels by value.
     c->cfg.small = nullptr;

@@ -64,7 +64,7 @@ struct rtw_ctx {
     int opt_small_static = 1;        // small scenes: rects and spheres in the static table (layout.h SmallGroup)
     int opt_shade_ctas = 3;          // k_shade_all<kCtas>: 2, 3 or 4 resident CTAs per SM
     int opt_walker = -1;             // -1 = auto (rtw_build_accel), 0 = flat kernels, 1 = persistent walkers
-    int opt_step_nodes = 8, opt_step_prims = 8, opt_min_active = 22;   // measured best on the Book-2 scene (tools/sweep_walk.sh)          // 0 = auto (rtw_build_accel), else 1..32
+    int opt_step_nodes = 4, opt_step_prims = 8, opt_min_active = 12;   // walkers: measured best with binned rays (tools/sweep_walk{3,4,5}.sh; round 1, slot order: 16 / 8 / 22)
     int opt_stream = -1;             // -1 = auto (rtw_build_accel), 0 = slot pool, 1 = streaming wavefront
     int opt_grid_pct = 100;          // share of the resident-CTA grids one context launches (two contexts on one GPU: 50)
     int opt_waves = 0;               // 0 = auto (rtw_render.cu), else 1..4 concurrent pools per frame

@@ -335,6 +335,6 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             rh, _ = o.trace_closest(director.camera_rays(0), 1)
             assert np.array_equal(hits, rh)
     finally:
-        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 8, "step_prims": 8, "min_active": 22,
+        for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 4, "step_prims": 8, "min_active": 12,
                      "tail_paths": 131072, "node_min": 0, "prim_min": 0, "sort_rays": -1, "sort_obits": 5, "sort_dbits": 1}.items():
             director.set_option(k, v)
