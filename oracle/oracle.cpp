@@ -639,15 +639,7 @@ extern "C" int orc_bvh_build(orc_scene* s) {
 }
 
 extern "C" void orc_bvh_set_leaf_size(orc_scene* s, int leaf_size) {
-    if (leaf_size <= 0) {   // the product's default (rtw_build_accel): one range for <= 16 primitives; plain leaves where it uses
-                            // its persistent walkers (an NEE stage, or more than 16 384 primitives); ranges of <= 4 elsewhere
-        const int n = (int)s->prims.size();
-        bool lambertian = false;
-        for (const rtw_prim& p : s->prims) lambertian |= s->mats[p.material].type == RTW_MAT_LAMBERTIAN;
-        const bool nee_stage = !s->lights.empty() && s->has_light_rect && lambertian;
-        const bool walker = n > 16384 || (nee_stage && n > 16);
-        leaf_size = n <= 16 ? 16 : (walker ? 1 : 4);
-    }
+    if (leaf_size <= 0) leaf_size = (int)s->prims.size() <= 16 ? 16 : 1;   // the product's default (rtw_build_accel): one range, else plain leaves
     s->leaf_size = leaf_size > 32 ? 32 : leaf_size;
 }
 

@@ -388,12 +388,13 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // of <= 4 primitives, which trades a few extra primitive tests for fewer node visits.
     // (the walker rule explained at the traversal-variant block below; decided here because the leaf size follows it)
     const bool nee_stage_pre = c->scene.n_lights > 0 && c->scene.has_light_rect && (c->class_mask & (1u << RTW_Q_LAMBERTIAN));
-    const bool walker_pre = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 16384 || (nee_stage_pre && n > RTW_SMALL_MAX));
-    // Walker scenes: plain LBVH leaves.  With the rays arriving bin by bin the node visits run at good lane counts and the
-    // primitive tests of a range (mixed kinds, some lanes with 1 and some with 4 primitives) are what diverges: leaf
-    // size 1 against 4 is +8 % on scene 4, +30 % / +45 % on the stress scenes of 2^20 / 2^17 primitives
-    // (profiles/r02/lbvh_r02.md, tools/sweep_walk{3,4,5}.sh).  The flat / streaming kernels keep 4.
-    b.leaf_size = c->opt_leaf_size > 0 ? c->opt_leaf_size : (n <= 16 ? 16 : (walker_pre ? 1 : 4));
+    const bool walker_pre = c->opt_walker >= 0 ? c->opt_walker != 0 : (n > 262144 || (nee_stage_pre && n > RTW_SMALL_MAX));
+    // Plain LBVH leaves (leaf size 1) for every scene that is walked through the hierarchy: under a 4-wide node a leaf
+    // range saves no fetch, and the primitive tests of a range are what diverges (mixed kinds; lanes with 1 and lanes
+    // with 4 primitives).  Leaf size 1 against round 1's 4 (tuned on the two-child walk), profiles/r02/lbvh_r02.md,
+    // tools/sweep_walk{3,4,5}.sh, tools/gpu_auto_check{2,3}.sh: walkers +8 % on scene 4, +30 % / +45 % on the stress
+    // scenes of 2^20 / 2^17 primitives; streaming wavefront +11 % on the Book-1 scene, +34 % / +66 % at 2048 / 16 384.
+    b.leaf_size = c->opt_leaf_size > 0 ? c->opt_leaf_size : (n <= 16 ? 16 : 1);
     c->leaf_size = b.leaf_size;
     const bool wide = c->opt_wide != 0 && n > b.leaf_size;
     b.wide = wide ? c->wide_nodes : nullptr;
@@ -439,9 +440,9 @@ extern "C" int rtw_build_accel(rtw_ctx* c) {
     // they lost ~10 % to the flat kernels until the rays were taken bin by bin (round 2, option sort_rays,
     // profiles/r02/sort_rays_r02f.md): with the binning the walkers also win on the Book-2 spheres scene (520 primitives,
     // NEE: 975 against 901 Mpaths/s), while the Book-1 scene (528 primitives, no NEE) stays with the streaming
-    // wavefront (1635 against 1353); on the sky-lit stress scenes streaming leads up to 2^14 primitives (3244 against
-    // 3029 at 2048, 1524 against 1507 at 16 384) and falls behind above (491 against 592 at 2^17, 136 against 260 at 2^20).
-    // Auto: walkers above 16 384 primitives, and for every LBVH scene with an NEE stage.
+    // wavefront (1821 against 1493 with plain leaves); on the sky-lit stress scenes streaming leads up to 2^17 primitives
+    // (4297 against 3604 at 2048, 2533 against 2195 at 16 384, 984 against 842 at 2^17) and falls behind at 2^20 (281
+    // against 334).  Auto: walkers for every LBVH scene with an NEE stage, and above 2^18 primitives.
     c->cfg.walker = walker_pre;   // (decided before the build: the leaf size follows it)
     // Small scenes (one leaf range, <= RTW_SMALL_MAX leaves and transforms): the leaf records go to
     // the traversal kernels by value.

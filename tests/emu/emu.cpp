@@ -37,7 +37,7 @@ struct Emu {
 };
 
 extern "C" Emu* emu_create(const rtw_scene_desc* d, int max_top, int leaf_size) {
-    if (leaf_size <= 0) leaf_size = d->n_prims <= 16 ? 16 : 4;   // same default as rtw_build_accel
+    if (leaf_size <= 0) leaf_size = d->n_prims <= 16 ? 16 : 1;   // same default as rtw_build_accel
     if (leaf_size > RTW_MAX_LEAF_SIZE) leaf_size = RTW_MAX_LEAF_SIZE;
     Emu* e = new Emu();
     const int n = d->n_prims;
