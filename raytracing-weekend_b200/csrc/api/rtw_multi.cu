@@ -39,9 +39,17 @@ struct Nccl {
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool load() {
+        // First whatever NCCL the process already has (a host such as PyTorch brings its own copy, and a second
+        // library with the same soname cannot be loaded beside it); else the system's, kept out of the global
+        // symbol scope.  A host that imports PyTorch AFTER this call will find this copy under torch's soname:
+        // import it first.
         for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
-            lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            lib = dlopen(name, RTLD_NOW | RTLD_NOLOAD);
             if (lib) break;
+        }
+        for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+            if (lib) break;
+            lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
         }
         if (!lib) return false;
 #define RTW_NCCL_SYM(field, sym) field = reinterpret_cast<decltype(field)>(dlsym(lib, sym)); if (!field) return false;

@@ -12,6 +12,10 @@ import subprocess
 import numpy as np
 import pytest
 
+# PyTorch first: rtw_create_multi dlopens NCCL, and on a box with two or more GPUs the system's libnccl.so.2 would then
+# sit under the soname that torch's own, newer copy needs (ImportError: undefined symbol ncclDevCommCreate).
+torch = pytest.importorskip("torch")
+
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -70,7 +74,6 @@ def test_sharded_frame_equals_the_one_gpu_frame(director, rtw, orc, shard):
 
 def test_rows_entry_point_renders_only_its_rows(director, rtw, orc):
     """rtw_render_accum_rows: a tile leaves every other row of the accumulator untouched."""
-    torch = pytest.importorskip("torch")
     Nx, Ny = 64, 40
     director.init(Nx, Ny, 1)
     director.createScene(3)

@@ -320,7 +320,7 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
                      # the walkers take the rays in (origin cell, direction bin) order instead of slot order
                      {"walker": 1, "stream": 0, "small": 0, "step_nodes": 8, "node_min": 0, "prim_min": 0, "min_active": 22, "sort_rays": 1},
                      {"walker": 1, "sort_rays": 2, "sort_obits": 3, "sort_dbits": 2}, {"walker": 1, "sort_rays": 2, "sort_obits": 5, "sort_dbits": 1},
-                     {"walker": 1, "sort_rays": 0}):
+                     {"walker": 1, "sort_rays": 0}, {"walker": 1, "sort_rays": 1, "sort_camera": 0}):
             for k, v in opts.items():
                 director.set_option(k, v)
             director.createScene(sid)
@@ -336,5 +336,5 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
             assert np.array_equal(hits, rh)
     finally:
         for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 4, "step_prims": 8, "min_active": 12,
-                     "tail_paths": 131072, "node_min": 0, "prim_min": 0, "sort_rays": -1, "sort_obits": 5, "sort_dbits": 1}.items():
+                     "tail_paths": 131072, "node_min": 0, "prim_min": 0, "sort_rays": -1, "sort_obits": 5, "sort_dbits": 1, "sort_camera": 1}.items():
             director.set_option(k, v)
