@@ -244,7 +244,8 @@ int  rtw_build_accel(rtw_ctx* ctx);
 /* Synchronous.  rgba_out_host: caller-owned Nx*Ny*4 floats, row 0 = bottom row,
  * sqrt-gamma encoded, alpha 1 (raygen/raygen.cu:151-158).  spp == 1 reproduces
  * the reference launch (Q1); spp > 1 averages samples k = 0..spp-1 whose seeds
- * are tea<64>(pixel, k). */
+ * are tea<64>(pixel, k).  Option "seed_base" = b shifts the range to k = b..b+spp-1
+ * (SURVEY.md §8b seed_base: disjoint ranges give independent estimates). */
 int  rtw_render(rtw_ctx* ctx, int Nx, int Ny, int spp, int max_depth,
                 float* rgba_out_host);
 

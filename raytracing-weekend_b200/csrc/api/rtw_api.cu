@@ -151,6 +151,9 @@ extern "C" int rtw_set_option(rtw_ctx* c, const char* name, int64_t value) {
     } else if (!strcmp(name, "sort_rays")) {
         if (value < -1 || value > 2) return fail(c, RTW_ERR_INVALID, "sort_rays out of range [-1, 2]");
         c->opt_sort_rays = (int)value;
+    } else if (!strcmp(name, "seed_base")) {
+        if (value < 0 || value > 0x3fffffff) return fail(c, RTW_ERR_INVALID, "seed_base out of range [0, 2^30)");
+        c->opt_seed_base = (int)value;
     } else if (!strcmp(name, "sort_camera")) {
         c->opt_sort_camera = value != 0;
     } else if (!strcmp(name, "sort_obits") || !strcmp(name, "sort_dbits")) {

@@ -83,6 +83,7 @@ struct rtw_ctx {
     int opt_sort_camera = 1;         // camera rays get direction bins of their own (6 x 256 x 256 on a cube map)
     int opt_sort_obits = 5, opt_sort_dbits = 1;   // bits per axis of the origin cell / of the direction bin (obits + dbits <= 6: 2^18 bins)
     float key_lo[3] = {0, 0, 0}, key_hi[3] = {0, 0, 0};   // bounds of the primitive centroids (rtw_build_accel): the cells of the ray keys
+    int opt_seed_base = 0;           // rtw_render: index of the frame's first sample (SURVEY §8b seed_base)
     int opt_profile = 0;
     int opt_lag = 3;
 

@@ -317,7 +317,9 @@ extern "C" int rtw_render(rtw_ctx* c, int Nx, int Ny, int spp, int max_depth, fl
         c->frame_pixels = npix;
     }
     RTW_CUDA(c, cudaMemsetAsync(c->d_accum, 0, sizeof(float4) * npix, c->stream));
-    int rc = rtw_render_accum(c, Nx, Ny, 0, 1, spp, max_depth, reinterpret_cast<float*>(c->d_accum));
+    // option seed_base (SURVEY.md §8b `seed_base`): the frame's samples are k = seed_base .. seed_base + spp - 1, each
+    // seeded tea<64>(pixel, k) — two frames with disjoint ranges are independent estimates of the same image
+    int rc = rtw_render_accum(c, Nx, Ny, c->opt_seed_base, 1, spp, max_depth, reinterpret_cast<float*>(c->d_accum));
     if (rc != RTW_OK) return rc;
     c->frame_spp = spp;
     uint64_t l = 0;

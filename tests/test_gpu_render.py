@@ -338,3 +338,24 @@ def test_traversal_variants_give_the_same_bits(director, orc, sid, Nx, Ny):
         for k, v in {"stream": -1, "shade_ctas": 3, "walker": -1, "small": -1, "step_nodes": 4, "step_prims": 8, "min_active": 12,
                      "tail_paths": 131072, "node_min": 0, "prim_min": 0, "sort_rays": -1, "sort_obits": 5, "sort_dbits": 1, "sort_camera": 1}.items():
             director.set_option(k, v)
+
+
+def test_seed_base_shifts_the_sample_range(director, orc):
+    """SURVEY §8b `seed_base`: rtw_render with option seed_base = b renders samples b .. b + spp - 1; one sample is the
+    oracle's sample b bit for bit, and two disjoint ranges are different estimates of the same image."""
+    Nx, Ny = 64, 48
+    director.init(Nx, Ny, 1)
+    director.createScene(0)
+    o = orc.OracleScene(director.scene.desc, 13)
+    try:
+        director.set_option("seed_base", 5)
+        director.renderFrame(1)
+        ref5, _ = o.render(Nx, Ny, 1, mode=0, sample_first=5)
+        assert np.array_equal(director.linear().view(np.uint32), ref5.view(np.uint32))
+        director.set_option("seed_base", 0)
+        director.renderFrame(1)
+        ref0, _ = o.render(Nx, Ny, 1, mode=0)
+        assert np.array_equal(director.linear().view(np.uint32), ref0.view(np.uint32))
+        assert not np.array_equal(ref0, ref5)
+    finally:
+        director.set_option("seed_base", 0)
