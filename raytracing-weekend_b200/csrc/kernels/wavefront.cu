@@ -390,9 +390,10 @@ __device__ __forceinline__ uint32_t ray_key(const DWave& w, float3 o, float3 d) 
     for (int b = 0; b < w.key_obits; b++) m |= (((ix >> b) & 1u) << (3 * b + 2)) | (((iy >> b) & 1u) << (3 * b + 1)) | (((iz >> b) & 1u) << (3 * b));
     const float dm = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fmaxf(fabsf(d.z), 1e-30f));
     const float half = (float)(1 << (w.key_dbits - 1)), dtop = (float)((1 << w.key_dbits) - 1);
-    const uint32_t qx = (uint32_t)fminf(fmaxf((d.x / dm + 1.0f) * half, 0.f), dtop);
-    const uint32_t qy = (uint32_t)fminf(fmaxf((d.y / dm + 1.0f) * half, 0.f), dtop);
-    const uint32_t qz = (uint32_t)fminf(fmaxf((d.z / dm + 1.0f) * half, 0.f), dtop);
+    const float rdm = __frcp_rn(dm);   // (a key is a heuristic: no IEEE divisions here)
+    const uint32_t qx = (uint32_t)fminf(fmaxf((d.x * rdm + 1.0f) * half, 0.f), dtop);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((d.y * rdm + 1.0f) * half, 0.f), dtop);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((d.z * rdm + 1.0f) * half, 0.f), dtop);
     return (m << (3 * w.key_dbits)) | (qx << (2 * w.key_dbits)) | (qy << w.key_dbits) | qz;
 }
 // Camera rays (depth 0) all leave one point: their cell says nothing and an octant holds the whole image, so they get
@@ -405,36 +406,57 @@ __device__ __forceinline__ uint32_t camera_key(float3 d) {
     if (ax >= ay && ax >= az) { face = d.x < 0.f ? 1u : 0u; m = ax; u = d.y; v = d.z; }
     else if (ay >= az) { face = d.y < 0.f ? 3u : 2u; m = ay; u = d.x; v = d.z; }
     else { face = d.z < 0.f ? 5u : 4u; m = az; u = d.x; v = d.y; }
-    m = fmaxf(m, 1e-30f);
-    const uint32_t iu = (uint32_t)fminf(fmaxf((u / m + 1.0f) * 128.0f, 0.f), 255.f);
-    const uint32_t iv = (uint32_t)fminf(fmaxf((v / m + 1.0f) * 128.0f, 0.f), 255.f);
+    const float rm = __frcp_rn(fmaxf(m, 1e-30f));
+    const uint32_t iu = (uint32_t)fminf(fmaxf((u * rm + 1.0f) * 128.0f, 0.f), 255.f);
+    const uint32_t iv = (uint32_t)fminf(fmaxf((v * rm + 1.0f) * 128.0f, 0.f), 255.f);
     return (face << 16) | (iu << 8) | iv;
 }
+// Four items per thread (i, i + 256, i + 512, i + 768 of the CTA's 1024): the kernel is bound by memory latency
+// (ncu: long-scoreboard 41 warps per issue with one item per thread), so all loads are issued before any key is formed.
+constexpr int kBinItems = 4;
 template <bool kShadow>
 __global__ void __launch_bounds__(kBlock) k_ray_bin(const DWave w) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = kShadow ? w.counters[RTW_C_SHADOW] : (uint32_t)w.P;
-    if (i - lane >= n) return;   // whole warps only: the vote below needs every lane
-    uint32_t key = 0x80000000u | lane;   // no ray: a key of its own (matches no other lane), not binned
-    if (i < n) {
-        if (kShadow) {
-            key = ray_key(w, f3(w.sh_o[i]), f3(w.sh_d[i]));
-        } else {
-            const RayRec ray = w.rec[i].ray;
-            if (f2u(ray.o.w) != RTW_RAY_NONE) {
-                const bool primary = w.key_camera && misc_depth(w.rec[i].st.misc.x) == 0u;   // (the same 64-byte line)
-                key = primary ? (1u << (3 * (w.key_obits + w.key_dbits))) + camera_key(f3(ray.d)) : ray_key(w, f3(ray.o), f3(ray.d));
+    const uint32_t first = blockIdx.x * (kBlock * kBinItems) + threadIdx.x;
+    if (first - lane >= n) return;   // the CTA's first row of warps is past the end: so are the others
+    float4 o[kBinItems], d[kBinItems];
+    uint32_t depth[kBinItems];
+#pragma unroll
+    for (int k = 0; k < kBinItems; k++) {
+        const uint32_t i = first + k * kBlock;
+        o[k] = make_float4(0.f, 0.f, 0.f, u2f(RTW_RAY_NONE));
+        d[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        depth[k] = 1u;
+        if (i < n) {
+            if (kShadow) {
+                o[k] = w.sh_o[i];
+                d[k] = w.sh_d[i];
+            } else {
+                const RayRec ray = w.rec[i].ray;
+                o[k] = ray.o;
+                d[k] = ray.d;
+                depth[k] = misc_depth(w.rec[i].st.misc.x);   // (the same 64-byte line)
             }
         }
     }
-    const uint32_t peers = __match_any_sync(0xffffffffu, key);
-    const int leader = __ffs(peers) - 1;
-    uint32_t base = 0;
-    const bool binned = !(key & 0x80000000u);
-    if (binned && (int)lane == leader) base = atomicAdd(w.bins + key, (uint32_t)__popc(peers));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (i < n) w.bin_rank[i] = make_uint2(key, base + (uint32_t)__popc(peers & ((1u << lane) - 1u)));
+#pragma unroll
+    for (int k = 0; k < kBinItems; k++) {
+        const uint32_t i = first + k * kBlock;
+        if (i - lane >= n) break;        // whole warps only: the vote below needs every lane
+        uint32_t key = 0x80000000u | lane;   // no ray: a key of its own (matches no other lane), not binned
+        if (i < n && (kShadow || f2u(o[k].w) != RTW_RAY_NONE)) {
+            const bool primary = !kShadow && w.key_camera && depth[k] == 0u;
+            key = primary ? (1u << (3 * (w.key_obits + w.key_dbits))) + camera_key(f3(d[k])) : ray_key(w, f3(o[k]), f3(d[k]));
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        const bool binned = !(key & 0x80000000u);
+        if (binned && (int)lane == leader) base = atomicAdd(w.bins + key, (uint32_t)__popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (i < n) w.bin_rank[i] = make_uint2(key, base + (uint32_t)__popc(peers & ((1u << lane) - 1u)));
+    }
 }
 // bins: counts -> first positions, in two launches of n_bins / 1024 CTAs (a one-CTA scan of 2^18 bins is a chain of
 // 512 dependent L2 accesses per thread: 0.5 ms).  part[] = the sums of the 1024-bin chunks, behind bins[n_bins].
@@ -497,7 +519,7 @@ cudaError_t bin_rays(cudaStream_t s, const DWave& w, uint64_t* launches) {
     cudaError_t e = cudaMemsetAsync(w.bins, 0, sizeof(uint32_t) * (size_t)(n_bins + 1), s);
     if (e != cudaSuccess) return e;
     const int grid = (w.P + kBlock - 1) / kBlock;
-    k_ray_bin<kShadow><<<grid, kBlock, 0, s>>>(w);
+    k_ray_bin<kShadow><<<(w.P + kBlock * kBinItems - 1) / (kBlock * kBinItems), kBlock, 0, s>>>(w);
     k_bin_sum<<<(n_bins + 1023) / 1024, 1024, 0, s>>>(w);
     k_bin_scan<<<(n_bins + 1023) / 1024, 1024, 0, s>>>(w);
     k_ray_place<kShadow><<<grid, kBlock, 0, s>>>(w);
