@@ -484,7 +484,12 @@ def main():
         for name in stages:
             stages[name]["traffic"] = traffic_tab.get(name)
             stages[name]["share_of_kernel_time"] = stages[name]["ms_per_iteration"] / max(ksum, 1e-12)
-        dom = max(stages, key=lambda k: stages[k]["ms_per_iteration"])
+        # The kernel the HBM roof is reported for: the stage that moves the most algorithmic HBM bytes per iteration (on
+        # C2 k_shade*: 147 B x 2.0 M vertices against 44 B x 2.0 M rays of k_traverse).  It is also the longest launch
+        # under ncu (41 % of the serialised kernel time, profiles/r02/r02g_launch_list_summary.txt); live, with two waves,
+        # its CUDA-event time and the (issue-bound) traversal launch's are within a few per cent of each other, and picking
+        # "the longest" would flip between them from run to run.
+        dom = max(stages, key=lambda k: (stages[k]["units_per_iteration"] * stages[k]["bytes_per_unit"], stages[k]["ms_per_iteration"]))
         ds = stages[dom]
         step_bytes = sum(v["units_per_iteration"] * v["bytes_per_unit"] for v in stages.values()) * iters
         step_gbs = step_bytes / max(agg["render_ms"] * 1e-3, 1e-9) / 1e9
@@ -494,7 +499,8 @@ def main():
                             "avg_launch_ms": ds["ms_per_iteration"],
                             "step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_frame": step_bytes / max(args.steps, 1),
                                      "note": "all stages' algorithmic HBM bytes / device time of the timed frames"},
-                            "note": "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured live with CUDA "
+                            "note": "kernel = the stage that moves the most algorithmic HBM bytes per iteration.  "
+                                    "achieved = algorithmic HBM bytes per launch (DESIGN.md 4.2) / average launch time measured live with CUDA "
                                     "events on wave 0's stream inside the timed frames; with %d waves a launch shares the device with the other "
                                     "waves' launches, so per-launch figures understate what the GPU moves: `step` is the whole frame against the "
                                     "same roof, `alone` the same kernel timed with one wave.  traffic = dram bytes of one launch from the committed "
