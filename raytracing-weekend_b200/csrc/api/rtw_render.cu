@@ -121,7 +121,12 @@ extern "C" int rtw_render_accum_rows(rtw_ctx* c, int Nx, int Ny, int row_first, 
     // Pool size (measured on the B200, tools/diag_tail.py, C2 at 32-1024 spp): 2^22 slots in total is the fastest
     // at every frame length from 64 spp (23 M paths) up; 2^24 slots lose 28 % (the gathers through the queues then
     // span 2.7 GB).  Option pool_paths overrides (slots per wave).
-    const long long P_all = total >= (1ull << 23) ? (1ll << 22) : (1ll << 21);
+    // Round 2 (tools/sweep_c2_pool.sh, after the hit record moved into the slot record): on the by-value small scenes a
+    // frame of >= 2^28 paths (C2: 3.7e8) is 3 % faster with 2.75 M slots per wave (3003 / 3024 against 2926 / 2900
+    // Mpaths/s, two runs each; 2.25 M: 2824, 3 M: 2938, 4 M: 3015); the 128 spp share of one GPU of eight is not
+    // (2737 against 2770 with 2.5 M), so shorter frames keep 2^22 in total.
+    long long P_all = total >= (1ull << 23) ? (1ll << 22) : (1ll << 21);
+    if (c->cfg.small && !c->cfg.stream && total >= (1ull << 28)) P_all = 2ll * 2883584;
     struct Run {
         unsigned long long total = 0;
         uint64_t iter = 0;
