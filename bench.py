@@ -482,7 +482,11 @@ def main():
                             "gbs": gbs, "frac": gbs / peak, "kernel_ms_over_render_ms": ms / max(agg["render_ms"], 1e-9)}
         ksum = sum(v["ms_per_iteration"] for v in stages.values())
         for name in stages:
-            stages[name]["traffic"] = traffic_tab.get(name)
+            t = traffic_tab.get(name)
+            cap_pool = traffic_doc.get("pool_slots")
+            # the capture was taken with pools of `pool_slots`; a steady-state launch covers a pool, so the bytes of a
+            # launch scale with the pool this run used (C2 at 1024 spp: 2.75 M slots per wave, capture: 2^21)
+            stages[name]["traffic"] = (int(t * pool / cap_pool) if (t and cap_pool and pool != cap_pool) else t)
             stages[name]["share_of_kernel_time"] = stages[name]["ms_per_iteration"] / max(ksum, 1e-12)
         # The kernel the HBM roof is reported for: the stage that moves the most algorithmic HBM bytes per iteration (on
         # C2 k_shade*: 147 B x 2.0 M vertices against 44 B x 2.0 M rays of k_traverse).  It is also the longest launch
@@ -494,7 +498,9 @@ def main():
         step_bytes = sum(v["units_per_iteration"] * v["bytes_per_unit"] for v in stages.values()) * iters
         step_gbs = step_bytes / max(agg["render_ms"] * 1e-3, 1e-9) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ds["gbs"], "peak": peak, "unit": "GB/s",
-                            "frac": ds["frac"], "traffic": ds["traffic"], "traffic_source": traffic_doc.get("source"),
+                            "frac": ds["frac"], "traffic": ds["traffic"],
+                            "traffic_source": (traffic_doc.get("source") or "") + ("; scaled by %d / %d slots per pool" % (pool, traffic_doc.get("pool_slots"))
+                                                                                  if traffic_doc.get("pool_slots") and pool != traffic_doc.get("pool_slots") else ""),
                             "peak_source": peak_src, "bytes_per_unit": ds["bytes_per_unit"], "units_per_launch": ds["units_per_iteration"],
                             "avg_launch_ms": ds["ms_per_iteration"],
                             "step": {"achieved": step_gbs, "frac": step_gbs / peak, "bytes_per_frame": step_bytes / max(args.steps, 1),
